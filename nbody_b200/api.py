@@ -1,0 +1,188 @@
+"""The reference's Python call surface, numpy in / numpy out, float64 at
+the boundary, every function executed by the sm_100a kernels behind include/nbody_b200.h.
+
+    cic_density(positions, boxsize, N)                      FraP_kTilDelta.py:94
+    cic_assign(delta, coords, dx, Nmesh)                    Plotter.py:129
+    compute_delta(density)                                  FraP_kTilDelta.py:126
+    cic_window_ft(ngrid, boxsize)                           FraP_kTilDelta.py:73
+    deconvolve_cic(delta_grid, boxsize, ngrid)              FraP_kTilDelta.py:87
+    compute_power_spectrum_from_snapshot(path, L, Nmesh, deconvolve, use_fac)
+                                                            Power_compare.py:135
+    compute_power_spectrum(delta_x, fromcic, kx, ky, kz, L, N, withfac)
+                                                            Power_compare.py:422
+    read_positions / read_boxsize                           FraP_kTilDelta.py:55,63
+
+`precision` selects the device storage of grids: "f32" (default, the performance path;
+tolerances in DESIGN.md) or "f64" (parity mode; float64 grids, D2Z/Z2D cuFFT).
+Errors are Python exceptions like the reference's (ValueError for bad input).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import tables
+from .engine import default_engine
+from .snapshot import read_boxsize, read_positions  # noqa: F401  (part of the surface)
+
+_DT = {"f32": torch.float32, "f64": torch.float64}
+
+
+def _dtype(precision):
+    try:
+        return _DT[precision]
+    except KeyError:
+        raise ValueError("precision must be 'f32' or 'f64'") from None
+
+
+def _positions(positions):
+    p = np.ascontiguousarray(positions, dtype=np.float64)
+    if p.ndim != 2 or p.shape[1] != 3:
+        raise ValueError("positions must have shape (Np, 3)")
+    return p
+
+
+def _out(t: torch.Tensor) -> np.ndarray:
+    """device grid -> float64 numpy (the reference returns float64 arrays)."""
+    return t.to(torch.float64).cpu().numpy()
+
+
+# --------------------------------------------------------------------------------- a1
+def cic_density(positions, boxsize, N, precision="f32", return_index=False):
+    eng = default_engine()
+    pos = eng.to_device(_positions(positions))
+    dbg = torch.empty(pos.shape, dtype=torch.int32, device=eng.device) if return_index else None
+    grid = eng.cic_deposit(pos, boxsize / N, int(N), dtype=_dtype(precision), dbg_index=dbg)
+    if return_index:
+        return _out(grid), dbg.cpu().numpy()
+    return _out(grid)
+
+
+def cic_assign(delta, coords, dx, Nmesh, precision=None):
+    """In place like Plotter.py:128-145; the grid keeps its dtype (float32 or float64)."""
+    if not isinstance(delta, np.ndarray) or delta.shape != (Nmesh,) * 3:
+        raise ValueError("delta must be an (Nmesh,)*3 numpy array")
+    if precision is None:
+        precision = "f32" if delta.dtype == np.float32 else "f64"
+    eng = default_engine()
+    pos = eng.to_device(_positions(coords))
+    g = eng.to_device(np.ascontiguousarray(delta), None).to(_dtype(precision))
+    eng.cic_deposit(pos, float(dx), int(Nmesh), out=g, accumulate=True)
+    delta[...] = g.cpu().numpy().astype(delta.dtype, copy=False)
+    return delta
+
+
+# --------------------------------------------------------------------------------- a2
+def compute_delta(density, precision="f32"):
+    eng = default_engine()
+    g = eng.to_device(np.ascontiguousarray(density)).to(_dtype(precision))
+    return _out(eng.compute_delta(g))
+
+
+# --------------------------------------------------------------------------------- a3
+def cic_window_ft(ngrid, boxsize, guard=True):
+    """Host table (float64), separable form of FraP_kTilDelta.py:73-84."""
+    s = tables.sinc_table(ngrid, boxsize)
+    W = ((s[:, None, None] * s[None, :, None]) * s[None, None, :]) ** 2
+    if guard:
+        W[W == 0] = 1.0
+    return W
+
+
+def deconvolve_cic(delta_grid, boxsize, ngrid, precision="f32", guard=True):
+    eng = default_engine()
+    g = eng.to_device(np.ascontiguousarray(delta_grid)).to(_dtype(precision))
+    if g.shape != (ngrid,) * 3:
+        raise ValueError("delta_grid must have shape (ngrid,)*3")
+    return _out(eng.deconvolve_cic(g, boxsize, int(ngrid), guard=guard))
+
+
+def snapshot_to_delta(positions, boxsize, ngrid, subtract_mean=False, precision="f32"):
+    """Feeder_pipe.py:174-195 in one resident pass: deposit -> delta -> deconvolve."""
+    eng = default_engine()
+    pos = eng.to_device(_positions(positions))
+    g = eng.cic_deposit(pos, boxsize / ngrid, int(ngrid), dtype=_dtype(precision))
+    eng.compute_delta(g)
+    eng.deconvolve_cic(g, boxsize, int(ngrid), guard=True)
+    if subtract_mean:
+        # delta -= delta.mean()   (Feeder_pipe.py:193)
+        eng.grid_affine(g, c=float(eng.grid_sum(g).item()) / g.numel())
+    return _out(g)
+
+
+# --------------------------------------------------------------------------------- a4
+def power_spectrum_from_positions(positions, L, Nmesh, deconvolve=False, use_fac=False,
+                                  variant="power_compare", precision="f32", return_counts=False):
+    """Body of compute_power_spectrum_from_snapshot after the snapshot read
+    (Power_compare.py:150-200; variants Plotter.py:153-202, 1vs2tlptplotter.py:84-116)."""
+    eng = default_engine()
+    p = _positions(positions)
+    npart = p.shape[0]
+    pos = eng.to_device(p)
+    Nmesh = int(Nmesh)
+    g = eng.cic_deposit(pos, L / Nmesh, Nmesh, dtype=_dtype(precision))
+    V = L ** 3
+    if variant == "power_compare":
+        if not use_fac:
+            eng.grid_affine(g, a=(L / Nmesh) ** 3, b=npart / (L ** 3), c=1.0)
+        else:
+            eng.grid_affine(g, c=1.0)
+        if deconvolve:
+            eng.deconvolve_cic(g, L, Nmesh, guard=False)
+        if use_fac:
+            fac = Nmesh ** 3 * np.sqrt(2 * np.pi / V)
+            norm = 1.0 / (fac ** 2)
+        else:
+            norm = V / (Nmesh ** 6)
+        edges, counts, sums = eng.power_spectrum_bins(g, L, Nmesh, 300, norm=norm, closed_last=True)
+    elif variant in ("plotter", "lpt"):
+        eng.grid_affine(g, a=npart / Nmesh ** 3, c=1.0)
+        edges, counts, sums = eng.power_spectrum_bins(
+            g, L, Nmesh, 300 if variant == "plotter" else 100, window_power=2, clip_mode=2, clip_val=1e-3,
+            norm=V / (Nmesh ** 6), closed_last=True, kq_form="piN_L")
+    else:
+        raise ValueError(f"unknown variant {variant!r}")
+    counts = counts.cpu().numpy()
+    sums = sums.cpu().numpy()
+    centers = 0.5 * (edges[:-1] + edges[1:])
+    valid = counts > 0
+    out = (centers[valid], sums[valid] / counts[valid])
+    return out + (counts,) if return_counts else out
+
+
+def compute_power_spectrum_from_snapshot(snapshot_path, L, Nmesh, deconvolve=False, use_fac=False,
+                                         variant="power_compare", precision="f32"):
+    pos = read_positions(snapshot_path)
+    return power_spectrum_from_positions(pos, L, Nmesh, deconvolve, use_fac, variant, precision)
+
+
+# --------------------------------------------------------------------------------- a5
+def compute_power_spectrum(delta_x, fromcic=False, kx=0, ky=0, kz=0, L=0, N=0, withfac=False,
+                           variant="power_compare", precision="f32", return_counts=False):
+    """kx, ky, kz are accepted for signature compatibility; the window is rebuilt from the
+    separable table (it is a function of N and L only)."""
+    eng = default_engine()
+    N = int(N)
+    g = eng.to_device(np.ascontiguousarray(delta_x)).to(_dtype(precision))
+    if g.shape != (N, N, N):
+        raise ValueError("delta_x must have shape (N,N,N)")
+    norm = 1.0
+    if withfac or variant == "cic3d":
+        fac = np.sqrt(2 * np.pi / L ** 3) * N ** 3
+        norm = 1.0 / fac ** 2
+    wp, cm, cv = 0, 0, 0.0
+    if fromcic:
+        if variant == "plotter":
+            wp, cm, cv = 1, 2, 0.1
+        elif variant == "cic3d":
+            wp, cm = 2, 1
+        else:
+            wp = 2
+    edges, counts, sums = eng.power_spectrum_bins(g, L, N, 300, window_power=wp, clip_mode=cm, clip_val=cv,
+                                                  norm=norm, closed_last=False, kq_form="piN_L")
+    counts = counts.cpu().numpy()
+    sums = sums.cpu().numpy()
+    centers = 0.5 * (edges[1:] + edges[:-1])
+    valid = counts > 0
+    out = (centers[valid], sums[valid] / counts[valid])
+    return out + (counts,) if return_counts else out

@@ -1,0 +1,62 @@
+"""Host-side float64 tables (numpy), computed exactly as the reference computes them and
+uploaded to the kernels: FFT wavenumbers, the separable CIC-window factor, the
+P(k) bin edges, and the k²-space decision thresholds that make device binning bit-exact.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def k_vals(N, L):
+    """`2*np.pi*np.fft.fftfreq(N, d=L/N)` — FraP_kTilDelta.py:74-75, Power_compare.py:179."""
+    return 2 * np.pi * np.fft.fftfreq(N, d=L / N)
+
+
+def sinc_table(N, L):
+    """`np.sinc(k_vals/(2*k_quist))`, `k_quist = np.pi*(d)**(-1)` — FraP_kTilDelta.py:77-80.
+    The 3-D window is W[i,j,k] = ((s[i]*s[j])*s[k])**2."""
+    d = L / N
+    k_quist = np.pi * (d) ** (-1)
+    return np.sinc(k_vals(N, L) / (2 * k_quist))
+
+
+def sinc_table_kq(N, L):
+    """Same factor with `k_quist = np.pi * N / L` (Power_compare.py:436-437, Plotter.py:157)."""
+    k_quist = np.pi * N / L
+    return np.sinc(k_vals(N, L) / (2 * k_quist))
+
+
+def pk_edges(N, L, n_edges=300):
+    """`np.logspace(np.log10(2π/L), np.log10(k_mag.max()), n_edges)` — Power_compare.py:
+    187-190; k_mag.max() formed as sqrt((kx²+ky²)+kz²) like numpy does."""
+    kv = k_vals(N, L)
+    k2max = (kv ** 2).max()
+    k_max = np.sqrt((k2max + k2max) + k2max)
+    k_min = 2 * np.pi / L
+    return np.logspace(np.log10(k_min), np.log10(k_max), n_edges)
+
+
+def sqrt_thresholds(edges):
+    """For each edge e: the smallest float64 x with np.sqrt(x) >= e.  Also returns the
+    smallest x with np.sqrt(x) > edges[-1].  sqrt is monotone and correctly rounded, so
+    `x >= thresh[e]`  <=>  `np.sqrt(x) >= edges[e]` for every float64 x >= 0."""
+    e = np.asarray(edges, dtype=np.float64)
+
+    def smallest(pred_ge):
+        x = e * e
+        for _ in range(64):                      # walk down while the predicate still holds
+            lower = np.nextafter(x, 0.0)
+            move = pred_ge(lower)
+            if not move.any():
+                break
+            x = np.where(move, lower, x)
+        for _ in range(64):                      # walk up until it holds
+            bad = ~pred_ge(x)
+            if not bad.any():
+                break
+            x = np.where(bad, np.nextafter(x, np.inf), x)
+        return x
+
+    thr = smallest(lambda x: np.sqrt(x) >= e)
+    thr_gt = smallest(lambda x: np.sqrt(x) > e)
+    return thr, float(thr_gt[-1])

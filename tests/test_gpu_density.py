@@ -1,0 +1,192 @@
+"""GPU parity: CIC deposit, overdensity, deconvolution and P(k) binning through the C-ABI
+(nbody_b200.api -> ctypes -> libnbody_b200.so) against the float64 oracle and the
+reference's golden vectors.
+
+Tolerances (north_star / SURVEY §8a'):
+  cell index (i,j,k)           exact
+  shell-bin counts             exact (np.histogram and np.digitize semantics)
+  CIC grid, delta              max|Δ| / max|ref| <= 1e-5   (float32 grid);  1e-12 (float64 grid)
+  binned P(k)                  per non-empty bin |ΔP|/P <= 1e-5
+"""
+import numpy as np
+import pytest
+
+from conftest import golden, zeldovich_particles
+from oracle import restate
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def api():
+    import torch
+    assert torch.cuda.is_available()
+    from nbody_b200 import api as _api
+    return _api
+
+
+def nrm(a, ref):
+    return np.abs(a - ref).max() / np.abs(ref).max()
+
+
+@pytest.mark.parametrize("tag", ["test1", "test57", "train1", "train200"])
+@pytest.mark.parametrize("prec,tol", [("f32", TOL), ("f64", 1e-12)])
+def test_golden_snapshot_to_delta(api, tag, prec, tol):
+    g = golden(f"snap_{tag}.npz")
+    d = api.snapshot_to_delta(g["pos"], float(g["boxsize"]), 32, subtract_mean=tag.startswith("train"),
+                              precision=prec)
+    assert d.dtype == np.float64 and d.shape == (32, 32, 32)
+    assert nrm(d, g["delta_golden"]) <= tol
+
+
+@pytest.mark.parametrize("N", [32, 64, 50])
+def test_deposit_index_exact_and_grid(api, snap_test1, N):
+    pos, L, _ = snap_test1
+    grid, idx = api.cic_density(pos, L, N, return_index=True)
+    ref_idx, _ = restate.cic_index_weight(pos, L, N)
+    assert np.array_equal(idx, ref_idx)
+    ref = restate.cic_density(pos, L, N)
+    assert nrm(grid, ref) <= TOL
+    assert abs(grid.sum() - pos.shape[0]) <= 1e-5 * pos.shape[0]
+    g64 = api.cic_density(pos, L, N, precision="f64")
+    assert nrm(g64, ref) <= 1e-13
+
+
+def test_deposit_edge_cases(api):
+    L, N = 500.0, 16
+    cell = L / N
+    # empty input
+    g = api.cic_density(np.zeros((0, 3)), L, N)
+    assert g.shape == (N, N, N) and not g.any()
+    # exactly on nodes, on the upper box edge, out of the box on both sides
+    pos = np.array([[0.0, 0.0, 0.0], [cell, 2 * cell, 3 * cell], [L, L, L], [L - 1e-9, 1e-9, L / 2],
+                    [-0.3 * cell, 5.2 * cell, -7.9 * cell], [L + 0.25 * cell, 2 * L + 1.0, -L - 3.0],
+                    [np.nextafter(L, 0), np.nextafter(cell, 0), np.nextafter(cell, L)]])
+    grid, idx = api.cic_density(pos, L, N, precision="f64", return_index=True)
+    ref_idx, _ = restate.cic_index_weight(pos, L, N)
+    assert np.array_equal(idx, ref_idx)
+    ref = restate.cic_density(pos, L, N)
+    assert np.abs(grid - ref).max() <= 1e-14
+    # ragged: a single particle
+    one = api.cic_density(pos[3:4], L, N, precision="f64")
+    assert np.abs(one - restate.cic_density(pos[3:4], L, N)).max() <= 1e-15
+
+
+def test_cic_assign_in_place_float32_and_float64(api, snap_test1):
+    pos, L, _ = snap_test1
+    N = 32
+    for dt in (np.float32, np.float64):
+        d = np.ones((N, N, N), dtype=dt)
+        out = api.cic_assign(d, pos, L / N, N)
+        assert out is d and d.dtype == dt
+        ref = restate.cic_assign(np.ones((N, N, N), dtype=np.float64), pos, L / N, N)
+        assert nrm(d.astype(np.float64), ref) <= (TOL if dt == np.float32 else 1e-13)
+
+
+def test_compute_delta_and_deconvolve(api, snap_test1):
+    pos, L, _ = snap_test1
+    dens = restate.cic_density(pos, L, 32)
+    d = api.compute_delta(dens, precision="f64")
+    assert np.abs(d - restate.compute_delta(dens)).max() <= 1e-13
+    assert abs(d.mean()) < 1e-12
+    ref = restate.deconvolve_cic(restate.compute_delta(dens), L, 32)
+    assert nrm(api.deconvolve_cic(d, L, 32, precision="f64"), ref) <= 1e-12
+    assert nrm(api.deconvolve_cic(d, L, 32, precision="f32"), ref) <= TOL
+
+
+@pytest.mark.parametrize("dec", [False, True])
+@pytest.mark.parametrize("fac", [False, True])
+def test_pk_snapshot_vs_reference_golden(api, snap_test1, dec, fac):
+    pos, L, _ = snap_test1
+    g = golden("ref_pk_snapshot.npz")
+    k, p, c = api.power_spectrum_from_positions(pos, L, 32, deconvolve=dec, use_fac=fac, return_counts=True)
+    kr, pr, cr = restate.power_spectrum_from_positions(pos, L, 32, deconvolve=dec, use_fac=fac,
+                                                       return_counts=True)
+    assert np.array_equal(c, cr)                       # bin counts bit-exact (histogram semantics)
+    assert c.sum() == 32 ** 3 - 1
+    assert np.array_equal(k, g[f"pc_dec{int(dec)}_fac{int(fac)}_k"])
+    assert np.abs(p / g[f"pc_dec{int(dec)}_fac{int(fac)}_p"] - 1).max() <= TOL
+    assert np.abs(p / pr - 1).max() <= TOL
+
+
+def test_pk_variants_and_finer_mesh(api, snap_test1):
+    pos, L, _ = snap_test1
+    g = golden("ref_pk_snapshot.npz")
+    k, p = api.power_spectrum_from_positions(pos, L, 64)
+    assert np.array_equal(k, g["pc_mesh64_k"])
+    assert np.abs(p / g["pc_mesh64_p"] - 1).max() <= TOL
+    gp = golden("snap_giant32pm.npz")
+    for variant in ("plotter", "lpt"):
+        k, p, c = api.power_spectrum_from_positions(gp["pos"], 1000.0, 32, variant=variant, return_counts=True)
+        kr, pr, cr = restate.power_spectrum_from_positions(gp["pos"], 1000.0, 32, variant=variant,
+                                                           return_counts=True)
+        assert np.array_equal(c, cr) and np.array_equal(k, kr)
+        assert np.abs(p / pr - 1).max() <= TOL
+        assert np.array_equal(k, g[f"{variant}_giant_k"])
+        # the reference's own 'plotter' run is float32 end to end (see test_oracle_golden)
+        assert np.abs(p / g[f"{variant}_giant_p"] - 1).max() <= (2e-3 if variant == "plotter" else TOL)
+
+
+def test_pk_field_digitize_semantics(api):
+    g = golden("ref_pk_field.npz")
+    L, N = 500.0, 16
+    for wf in (0, 1):
+        k, p, c = api.compute_power_spectrum(g["delta_x"], False, L=L, N=N, withfac=bool(wf), return_counts=True)
+        _, _, cr = restate.compute_power_spectrum(g["delta_x"], False, L, N, withfac=bool(wf), return_counts=True)
+        assert np.array_equal(c, cr) and c.sum() == N ** 3 - 2       # digitize drops k == k_max (Q3)
+        assert np.array_equal(k, g[f"pc_fft_fac{wf}_k"])
+        assert np.abs(p / g[f"pc_fft_fac{wf}_p"] - 1).max() <= TOL
+        k, p = api.compute_power_spectrum(g["delta_cic"], True, L=L, N=N, withfac=bool(wf))
+        assert np.array_equal(k, g[f"pc_cic_fac{wf}_k"])
+        assert np.abs(p / g[f"pc_cic_fac{wf}_p"] - 1).max() <= TOL
+    k, p = api.compute_power_spectrum(g["delta_cic"], True, L=L, N=N, variant="plotter")
+    assert np.array_equal(k, g["plotter_cic_k"])
+    assert np.abs(p / g["plotter_cic_p"] - 1).max() <= TOL
+    # float64 device path agrees to round-off
+    k, p = api.compute_power_spectrum(g["delta_cic"], True, L=L, N=N, precision="f64")
+    assert np.abs(p / g["pc_cic_fac0_p"] - 1).max() <= 1e-11
+
+
+@pytest.mark.parametrize("n,N", [(32, 64), (48, 96), (33, 45)])
+def test_zeldovich_set_deposit_and_pk(api, n, N):
+    L = 1000.0
+    pos = zeldovich_particles(n, L)
+    grid, idx = api.cic_density(pos, L, N, return_index=True)
+    ref_idx, _ = restate.cic_index_weight(pos, L, N)
+    assert np.array_equal(idx, ref_idx)
+    assert nrm(grid, restate.cic_density(pos, L, N)) <= TOL
+    k, p, c = api.power_spectrum_from_positions(pos, L, N, return_counts=True)
+    kr, pr, cr = restate.power_spectrum_from_positions(pos, L, N, return_counts=True)
+    assert np.array_equal(c, cr)
+    assert np.abs(p / pr - 1).max() <= TOL
+
+
+def test_full_size_properties_c2(api):
+    """BASELINE config 2 size (128^3 particles -> 256^3 mesh): size-independent properties."""
+    import torch
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    n, N, L = 128, 256, 1000.0
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    lat = torch.arange(n, device="cuda", dtype=torch.float64) * (L / n)
+    pos = torch.stack(torch.meshgrid(lat, lat, lat, indexing="ij"), -1).reshape(-1, 3)
+    pos = (pos + (torch.rand(pos.shape, generator=gen, device="cuda", dtype=torch.float64) - 0.5) * (L / n)) % L
+    pos = pos.contiguous()
+    grid = eng.cic_deposit(pos, L / N, N)
+    total = float(eng.grid_sum(grid).item())
+    assert abs(total - n ** 3) <= 1e-6 * n ** 3                    # mass conservation
+    g2 = eng.cic_deposit(pos.flip(0).contiguous(), L / N, N)       # order independence
+    assert float((grid - g2).abs().max()) <= 1e-5 * float(grid.abs().max())
+    eng.grid_affine(grid, a=n ** 3 / N ** 3, c=1.0)
+    edges, counts, sums = eng.power_spectrum_bins(grid, L, N, 300, norm=L ** 3 / N ** 6)
+    assert int(counts.sum()) == N ** 3 - 1                         # every k>0 mode lands in a bin
+    km = restate.k_mag_grid(N, L).ravel()
+    cr, _ = restate.shell_bin(km, np.ones_like(km), restate.pk_edges(N, L), closed_last=True)
+    assert np.array_equal(counts.cpu().numpy(), cr)                # counts are geometry only
+    # Parseval: sum over k>0 of |delta_k|^2 = N^3 * sum(delta^2) - |delta_0|^2
+    lhs = float(sums.sum()) / (L ** 3 / N ** 6)
+    d = grid.double()
+    rhs = float(N ** 3 * (d * d).sum() - d.sum() ** 2)
+    assert abs(lhs / rhs - 1) <= 1e-5
