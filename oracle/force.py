@@ -1,0 +1,125 @@
+"""TEST INFRASTRUCTURE ONLY — float64 CPU restatement of the PP / PM / P3M force step.
+
+PARITY UNPINNED: the reference has no source for this path.  The force solver is the
+external code CONCEPT (github.com/jmd-dk/concept, version unpinned — SURVEY §8c), called
+as a subprocess at TheFeedingPipeline/NeuNetværk_test.py:155-171 and SnapVsPK/Ucertain.py:
+89-97.  What follows is OUR specification (SURVEY §8a'), assembled from
+  * the reference's own primitives: cic_density (FraP_kTilDelta.py:93-123), cic_window_ft
+    (:73-84), the k grid 2π·fftfreq (CiC/3D startbetingelser1.py:69-72) and the
+    i·k/k² operator (:105-107);
+  * the reference's .param choices: Fourier differentiation, deconvolve (True, True),
+    interlace (True, True) (Different_Sizes/Giant.param:45-58, NN.param:55-61), P3M with
+    r_s = 1.25 cells and r_cut = 4.5 r_s (corroborated by the 5x5x5 tiling in the logs);
+  * the standard erfc / Gaussian force split and Plummer softening.
+The CUDA kernels are checked against this file; this file is checked against analytic
+properties in tests/test_force_oracle.py (Newton's third law, 1/r² at long range,
+PM + short-range = softened Newton, interlacing removes odd aliases).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+
+from . import restate
+
+
+# ------------------------------------------------------------------------------- PM
+def pm_kernel_tables(N, L, r_s=0.0, deconv_order=2):
+    """Per-axis tables: signed k (Nyquist zeroed for the gradient), k², and the separable
+    factor t = exp(-k² r_s²) / s^(2·deconv_order) with s the reference's sinc factor."""
+    kv = restate.k_vals(N, L)
+    kgrad = kv.copy()
+    if N % 2 == 0:
+        kgrad[N // 2] = 0.0            # a real field has no gradient at the Nyquist plane
+    s = restate.sinc_table(N, L)
+    t = np.exp(-(kv ** 2) * r_s ** 2) / s ** (2 * deconv_order)
+    return kv, kgrad, t
+
+
+def pm_accel_mesh(pos, L, N, G=1.0, mass=1.0, r_s=0.0, deconv_order=2, interlace=False):
+    """Long-range acceleration on the mesh, 3 x (N,N,N) float64.
+      rho      = mass * cic_density / cell³                        (a1)
+      g_k      = 4πG · (i k / k²) · rho_k · exp(-k² r_s²) / W^deconv_order,  g_0 = 0
+    (φ_k = -4πG ρ_k / k², g = -∇φ; i·k/k² is the reference's ψ operator.)
+    interlace: second deposit of positions shifted by +cell/2 in x,y,z, phase-corrected by
+    exp(+i k·s), averaged (upstream interlacing)."""
+    cell = L / N
+    kv, kgrad, t = pm_kernel_tables(N, L, r_s, deconv_order)
+    nzh = N // 2 + 1
+    rho_k = np.fft.rfftn(restate.cic_density(pos, L, N))
+    if interlace:
+        rho2 = np.fft.rfftn(restate.cic_density(pos + 0.5 * cell, L, N))
+        m = np.fft.fftfreq(N, d=1.0 / N)                      # signed integer frequencies
+        ph = np.exp(1j * np.pi * m / N)                        # exp(+i k_a cell/2)
+        if N % 2 == 0:
+            ph[N // 2] = 0.0      # Hermitian part of exp(±iπ/2): keeps the combined mesh real
+        phase = ph[:, None, None] * ph[None, :, None] * ph[None, None, :nzh]
+        rho_k = 0.5 * (rho_k + rho2 * phase)
+    k2 = (kv ** 2)[:, None, None] + (kv ** 2)[None, :, None] + (kv ** 2)[None, None, :nzh]
+    k2[0, 0, 0] = 1.0
+    filt = (t[:, None, None] * t[None, :, None] * t[None, None, :nzh]) / k2
+    filt[0, 0, 0] = 0.0
+    pref = 4.0 * math.pi * G * mass / cell ** 3
+    base = pref * filt * rho_k
+    gx = np.fft.irfftn(1j * kgrad[:, None, None] * base, s=(N, N, N), axes=(0, 1, 2))
+    gy = np.fft.irfftn(1j * kgrad[None, :, None] * base, s=(N, N, N), axes=(0, 1, 2))
+    gz = np.fft.irfftn(1j * kgrad[None, None, :nzh] * base, s=(N, N, N), axes=(0, 1, 2))
+    return gx, gy, gz
+
+
+def pm_accel(pos, L, N, **kw):
+    """Long-range acceleration at the particles: CIC gather (adjoint of the deposit)."""
+    g = pm_accel_mesh(pos, L, N, **kw)
+    return np.column_stack([restate.trilinear_gather(c, pos, L, N) for c in g])
+
+
+# ------------------------------------------------------------------------------- pair forces
+def split_factor(r, r_s):
+    """Short-range fraction of the Newtonian force: erfc(u) + 2u/sqrt(pi) exp(-u²), u = r/(2 r_s)."""
+    from scipy.special import erfc
+    u = r / (2.0 * r_s)
+    return erfc(u) + 2.0 * u / math.sqrt(math.pi) * np.exp(-u * u)
+
+
+def pp_accel(pos, L=None, G=1.0, mass=1.0, eps=0.0, periodic=False, i_subset=None, chunk=256):
+    """Softened direct sum: a_i = -G m Σ_j r_ij / (r² + ε²)^{3/2}, r_ij = x_i - x_j
+    (minimum image if periodic).  i_subset: indices of the i-particles to evaluate."""
+    idx = np.arange(pos.shape[0]) if i_subset is None else np.asarray(i_subset)
+    out = np.zeros((idx.size, 3))
+    for s in range(0, idx.size, chunk):
+        ii = idx[s:s + chunk]
+        d = pos[ii, None, :] - pos[None, :, :]
+        if periodic:
+            d -= L * np.round(d / L)
+        r2 = (d * d).sum(-1) + eps * eps
+        r2[r2 == 0.0] = np.inf
+        w = r2 ** -1.5
+        out[s:s + chunk] = -G * mass * (d * w[..., None]).sum(1)
+    return out
+
+
+def p3m_short_accel(pos, L, r_s, r_cut, G=1.0, mass=1.0, eps=0.0, i_subset=None, chunk=128):
+    """Short-range pair acceleration, minimum image, r < r_cut:
+       a_i = -G m Σ_j r_ij / (r²+ε²)^{3/2} · split_factor(r)."""
+    idx = np.arange(pos.shape[0]) if i_subset is None else np.asarray(i_subset)
+    out = np.zeros((idx.size, 3))
+    for s in range(0, idx.size, chunk):
+        ii = idx[s:s + chunk]
+        d = pos[ii, None, :] - pos[None, :, :]
+        d -= L * np.round(d / L)
+        r2 = (d * d).sum(-1)
+        inr = (r2 < r_cut * r_cut) & (r2 > 0)
+        r = np.sqrt(np.where(inr, r2, 1.0))
+        w = np.where(inr, split_factor(r, r_s) * (np.where(inr, r2, 1.0) + eps * eps) ** -1.5, 0.0)
+        out[s:s + chunk] = -G * mass * (d * w[..., None]).sum(1)
+    return out
+
+
+# ------------------------------------------------------------------------------- kick / drift
+def kick_drift(pos, mom, acc, L, mass=1.0, a=1.0, dt_kick=0.0, dt_drift=0.0):
+    """mom += m·g·Δt_kick ; pos += mom/(m a²)·Δt_drift ; pos %= L (Power_compare.py:391)."""
+    mom = mom + mass * acc * dt_kick
+    pos = pos + mom * (dt_drift / (mass * a * a))
+    pos %= L
+    return pos, mom
