@@ -114,6 +114,91 @@ int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec, const dou
                       int clip_mode, double clip_val, double norm, int closed_last,
                       int64_t* counts, double* sums, void* stream);
 
+/* ---- K7  Gaussian random field from P(k) ------------------------------------------------
+ * nb_hermitian_R replaces createR's symmetrisation loop (Cosmo data create (new).py:35-45;
+ * guarded copies CiC/3D startbetingelser1.py:82-93, Power_compare.py:301-312):
+ * R = c1 + i c2, R[0,0,0] real, then `R[-i,-j,-k] = conj(R[i,j,k])` in lexicographic order.
+ * c1, c2: N^3 float64 draws; R_out: N^3 complex128 (interleaved re,im).
+ * guard_selfconj = 1: `if (i,j,k) != (-i,-j,-k)` variant (self-conjugate points keep their
+ * imaginary part); 0: createR (imaginary part negated). */
+int nb_hermitian_R(nb_ctx* ctx, const double* c1, const double* c2, int N, int guard_selfconj,
+                   double* R_out, void* stream);
+/* nb_grf_synthesize replaces find_delta (Cosmo data create (new).py:114-137) and the δ / ψ
+ * block of CiC/3D startbetingelser1.py:98-112 (= Power_compare.py:316-331):
+ *   delta = ifftn(sqrt(P)·fac·R).real,  psi_a = ifftn(1j·k_a/k_mag²·sqrt(P)·fac·R).real
+ * with k_mag[0,0,0] = 1e-10.  pk_grid: N^3 float64 P(k) on the FFT grid (the caller
+ * evaluates its spectrum there; CLASS is not part of this library); k_vals: N float64;
+ * fac: sqrt(2π/L³)·N³ (or 1, Plotter.py:100).  delta_out (N^3) and psi_out (3·N^3) are
+ * float32/float64 by `prec`; either may be NULL. */
+int nb_grf_synthesize(nb_ctx* ctx, const double* pk_grid, const double* c1, const double* c2, int N,
+                      const double* k_vals, double fac, int guard_selfconj, int prec,
+                      void* delta_out, void* psi_out, void* stream);
+
+/* ---- K3  CIC gather, displacement, kick / drift -----------------------------------------
+ * nb_cic_gather: out[p,c] (=|+=) scale · Σ_8 w · field[c][cell]  with the deposit's float64
+ * index/weight math; true periodic trilinear interpolation, equal to the reference's
+ * RegularGridInterpolator where the reference evaluates it (lattice nodes,
+ * Power_compare.py:356-385).  field: ncomp·N^3 (`prec`), out: (Np,ncomp) f64. */
+int nb_cic_gather(nb_ctx* ctx, const void* field, int ncomp, int N, int prec, const double* pos,
+                  int64_t np, double cell, double shift, double scale, int accumulate, double* out,
+                  void* stream);
+/* pos <- (pos + disp) % L with Python-mod semantics: `particles += ψ; particles %= L`
+ * (Power_compare.py:386-391). */
+int nb_displace_wrap(nb_ctx* ctx, double* pos, const double* disp, int64_t np, double L, void* stream);
+/* mom += kick·acc ; pos <- (pos + drift·mom) % L   (kick = m·Δt_kick, drift = Δt_drift/(m a²);
+ * no reference source: CONCEPT-internal leapfrog). */
+int nb_kick_drift(nb_ctx* ctx, double* pos, double* mom, const double* acc, int64_t np, double kick,
+                  double drift, double L, void* stream);
+/* Fused PM tail: g = gscale · gather(force3 [, averaged with force3_shifted gathered at
+ * pos + cell/2]); acc_out (nullable) <- g; if mom != NULL: kick + drift + wrap as above. */
+int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                         double cell, double* pos, double* mom, double* acc_out, int64_t np,
+                         double gscale, double kick, double drift, double L, void* stream);
+
+/* ---- K2  PM / P3M long-range solve --------------------------------------------------------
+ * No reference source (CONCEPT-internal; configured by Different_Sizes/Giant.param:28-68,
+ * TheFeedingPipeline/NN.param:53-83).  Built from the reference's window
+ * (FraP_kTilDelta.py:73-84) and its i·k/k² operator (CiC/3D startbetingelser1.py:105-107):
+ *   g_k = pref · i k/k² · exp(-k² r_s²) / W^deconv_order · rho_k,  g_0 = 0, Nyquist
+ *   gradient zeroed; rho2 != NULL: upstream interlacing 0.5(rho1 + rho2·e^{+ik·s});
+ *   h3 != NULL: second set g·e^{-ik·s} for downstream interlacing.
+ * rho1/rho2: [N][N][N/2+1] complex64; g3/h3: 3 consecutive spectra of that shape. */
+int nb_kspace_fused(nb_ctx* ctx, const void* rho1, const void* rho2, int N, const double* k_vals,
+                    const double* sinc_tab, double r_s, int deconv_order, double pref, void* g3,
+                    void* h3, void* stream);
+/* deposit -> R2C -> [shifted deposit -> R2C] -> nb_kspace_fused -> 3 (6) C2R.
+ * force3 / force3_shifted: 3·N^3 float32 (unnormalised C2R: fold 1/N^3 into pref). */
+int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N,
+                     const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                     int interlace_up, int interlace_down, double pref, float* force3,
+                     float* force3_shifted, void* stream);
+
+/* ---- K4  PP direct sum -------------------------------------------------------------------
+ * No reference source (CONCEPT PP; only its run time is in PPPMP3M/pppmp3mplotter.py:18-19).
+ * nb_pp_pack: (Np,3) f64 -> float4 (x-ox, y-oy, z-oz, w); w = masses[p] or `mass`.
+ * nb_pp_accel: acc[i] (=|+=) scale · Σ_j w_j d/(|d|²+eps²)^{3/2}, d = x_j - x_i (minimum
+ * image if box > 0).  FP32 FMA + rsqrt in 512-particle j-tiles, FP64 across tiles.
+ * variant: 0 default, 1 scalar FFMA, 2 packed FFMA2 (4 i/thread), 3 packed (8 i/thread). */
+int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy, double oz, double mass,
+               const double* masses, void* out_xyzw, void* stream);
+int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
+                double eps, double box, double scale, int variant, int accumulate, double* acc,
+                void* stream);
+
+/* ---- K5  P3M short range -------------------------------------------------------------------
+ * No reference source (CONCEPT-internal; log lines 42-46, 89-95 show tiling + reordering).
+ * nb_cell_sort: counting sort into ncs^3 cells of side L/ncs; sorted_xyzw float4
+ * (cell-relative x,y,z, mass), perm[slot] = original index, cell_start[ncs^3+1].
+ * nb_p3m_short: for the cells [cell_lo, cell_hi) (slab of a multi-GPU run, or all):
+ *   acc[perm[i]] (=|+=) scale · Σ_{r<r_cut} w_j d/(r²+eps²)^{3/2}·(1 - u³Q(t)),
+ *   u = r/(2 r_s), t = 2u²/u_max² - 1, Q given by ncoef = 11 monomial coefficients (host). */
+int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
+                 void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream);
+int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
+                 int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
+                 double eps, const double* coef_host, int ncoef, double u_max, double scale,
+                 int accumulate, double* acc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

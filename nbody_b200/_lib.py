@@ -29,6 +29,21 @@ PROTOTYPES = {
     "nb_deconvolve_cic": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_i32, c_vp]),
     "nb_power_spectrum": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_f64, c_f64, c_f64, c_i32,
                                   c_i32, c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),
+    "nb_hermitian_R": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "nb_grf_synthesize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_f64, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "nb_cic_gather": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_vp, c_vp]),
+    "nb_displace_wrap": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f64, c_vp]),
+    "nb_kick_drift": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_f64, c_f64, c_f64, c_vp]),
+    "nb_gather_kick_drift": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_f64, c_vp, c_vp, c_vp, c_i64, c_f64, c_f64,
+                                     c_f64, c_f64, c_vp]),
+    "nb_kspace_fused": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp]),
+    "nb_pm_force_mesh": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_vp, c_f64, c_i32, c_i32, c_i32, c_f64,
+                                 c_vp, c_vp, c_vp]),
+    "nb_pp_pack": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_vp, c_vp]),
+    "nb_pp_accel": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_i32, c_vp, c_vp]),
+    "nb_cell_sort": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
+    "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
+                             c_f64, c_f64, c_i32, c_vp, c_vp]),
 }
 
 

@@ -186,3 +186,93 @@ def compute_power_spectrum(delta_x, fromcic=False, kx=0, ky=0, kz=0, L=0, N=0, w
     valid = counts > 0
     out = (centers[valid], sums[valid] / counts[valid])
     return out + (counts,) if return_counts else out
+
+
+# --------------------------------------------------------------------------------- a6
+def _draws(N, c1, c2, seed):
+    """c1 then c2 from the legacy global RNG like the reference (c1 drawn fully before c2)."""
+    if c1 is None or c2 is None:
+        if seed is not None:
+            np.random.seed(seed)
+        c1 = np.random.normal(0, 1 / np.sqrt(2), size=[N] * 3)
+        c2 = np.random.normal(0, 1 / np.sqrt(2), size=[N] * 3)
+    c1 = np.ascontiguousarray(c1, dtype=np.float64)
+    c2 = np.ascontiguousarray(c2, dtype=np.float64)
+    if c1.shape != (N, N, N) or c2.shape != (N, N, N):
+        raise ValueError("c1 and c2 must have shape (N,N,N)")
+    return c1, c2
+
+
+def createR(N, dim=3, mu=0, sig=1 / np.sqrt(2), c1=None, c2=None, seed=None, guard=False):
+    """Cosmo data create (new).py:24-47: Hermitian complex noise R (N,N,N) complex128.  The
+    draws come from numpy's legacy RNG on the host (bit-identical to the reference); the
+    symmetrisation loop runs on the GPU.  guard=True gives the `if`-guarded variant of
+    CiC/3D startbetingelser1.py:82-93."""
+    if dim != 3:
+        raise ValueError("only dim=3 is supported")
+    if c1 is None or c2 is None:
+        if seed is not None:
+            np.random.seed(seed)
+        c1 = np.random.normal(mu, sig, size=[N] * 3)
+        c2 = np.random.normal(mu, sig, size=[N] * 3)
+    c1, c2 = _draws(N, c1, c2, None)
+    eng = default_engine()
+    R = eng.hermitian_R(eng.to_device(c1), eng.to_device(c2), guard)
+    return R.cpu().numpy()
+
+
+# --------------------------------------------------------------------------------- a7
+def find_delta(z=None, L=None, N=None, A_s=None, n_s=None, omega_b=None, omega_cdm=None, *, Pk_grid=None,
+               c1=None, c2=None, seed=None, guard=False, use_fac=True, precision="f32"):
+    """Cosmo data create (new).py:114-137: δ = ifftn(sqrt(P)·fac·R).real.
+    CLASS is not part of this package: pass `Pk_grid`, P(k) evaluated on the (N,N,N) FFT grid
+    `k_mag` (with k_mag[0,0,0] = 1e-10 like the reference, :304-307); the cosmological
+    arguments are accepted for signature compatibility and ignored."""
+    if Pk_grid is None:
+        raise ValueError("find_delta needs Pk_grid (CLASS is not available in this package)")
+    N = int(N)
+    pk = np.ascontiguousarray(Pk_grid, dtype=np.float64).reshape(N, N, N)
+    c1, c2 = _draws(N, c1, c2, seed)
+    eng = default_engine()
+    delta, _ = eng.grf_synthesize(eng.to_device(pk), eng.to_device(c1), eng.to_device(c2), L, N, guard,
+                                  use_fac=use_fac, dtype=_dtype(precision), want_delta=True, want_psi=False)
+    return _out(delta)
+
+
+def grf_delta_psi(Pk_grid, L, N, c1=None, c2=None, seed=None, guard=True, precision="f32"):
+    """CLASS_simualtor without CLASS (Power_compare.py:279-331, CiC/3D startbetingelser1.py:
+    82-112): returns delta_x and (psi_x, psi_y, psi_z)."""
+    N = int(N)
+    pk = np.ascontiguousarray(Pk_grid, dtype=np.float64).reshape(N, N, N)
+    c1, c2 = _draws(N, c1, c2, seed)
+    eng = default_engine()
+    delta, psi = eng.grf_synthesize(eng.to_device(pk), eng.to_device(c1), eng.to_device(c2), L, N, guard,
+                                    dtype=_dtype(precision), want_delta=True, want_psi=True)
+    psi = _out(psi)
+    return _out(delta), (psi[0], psi[1], psi[2])
+
+
+# --------------------------------------------------------------------------------- a8
+def trilinear_gather(field, positions, L, N, precision="f64"):
+    """Periodic CIC gather of `field` ((N,N,N) or (ncomp,N,N,N)) at `positions`."""
+    eng = default_engine()
+    f = eng.to_device(np.ascontiguousarray(field)).to(_dtype(precision)).contiguous()
+    pos = eng.to_device(_positions(positions))
+    out = eng.cic_gather(f, pos, L / N, int(N)).cpu().numpy()
+    return out[:, 0] if np.ndim(field) == 3 else out
+
+
+def particle_assigment(psi, L, N, precision="f32", return_particles=False):
+    """Power_compare.py:336-418: lattice particles displaced by ψ (gathered at the lattice
+    nodes), wrapped with `particles %= L`, CIC-deposited, minus 1."""
+    N = int(N)
+    eng = default_engine()
+    x = np.linspace(0, L, N, endpoint=False)
+    lattice = np.array(np.meshgrid(x, x, x, indexing="ij")).reshape(3, -1).T
+    pos = eng.to_device(np.ascontiguousarray(lattice))
+    f = eng.to_device(np.ascontiguousarray(np.stack([np.asarray(p, dtype=np.float64) for p in psi])))
+    disp = eng.cic_gather(f.contiguous(), pos, L / N, N)            # ψ at the lattice nodes (exact)
+    eng.displace_wrap(pos, disp, L)
+    g = eng.cic_deposit(pos, L / N, N, dtype=_dtype(precision))
+    eng.grid_affine(g, c=1.0)
+    return (_out(g), pos.cpu().numpy()) if return_particles else _out(g)

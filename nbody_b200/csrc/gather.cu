@@ -1,0 +1,175 @@
+// K3 — trilinear (CIC) gather, displacement + wrap, and the fused gather + kick + drift.
+// The gather is the adjoint of K1 and uses the same float64 index / weight math
+// (FraP_kTilDelta.py:99-107), so deposit and gather address identical cells.
+// Reference call sites: RegularGridInterpolator at lattice nodes + `particles += ψ;
+// particles %= L` (Power_compare.py:356-391, CiC/3D startbetingelser1.py:137-173).
+#include "common.cuh"
+
+struct CicStencil {
+  int64_t r00, r01, r10, r11;
+  int k0, k1;
+  double w000, w001, w010, w011, w100, w101, w110, w111;
+};
+
+__device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, double cell, int N) {
+  CicStencil s;
+  const int i0 = nb_cell_index(x, cell, N), j0 = nb_cell_index(y, cell, N);
+  s.k0 = nb_cell_index(z, cell, N);
+  const double dx = nb_cell_frac(x, cell), dy = nb_cell_frac(y, cell), dz = nb_cell_frac(z, cell);
+  const int i1 = nb_wrap1(i0, N), j1 = nb_wrap1(j0, N);
+  s.k1 = nb_wrap1(s.k0, N);
+  const double wx0 = __dsub_rn(1.0, dx), wy0 = __dsub_rn(1.0, dy), wz0 = __dsub_rn(1.0, dz);
+  const double w00 = __dmul_rn(wx0, wy0), w01 = __dmul_rn(wx0, dy);
+  const double w10 = __dmul_rn(dx, wy0), w11 = __dmul_rn(dx, dy);
+  s.w000 = __dmul_rn(w00, wz0); s.w001 = __dmul_rn(w00, dz);
+  s.w010 = __dmul_rn(w01, wz0); s.w011 = __dmul_rn(w01, dz);
+  s.w100 = __dmul_rn(w10, wz0); s.w101 = __dmul_rn(w10, dz);
+  s.w110 = __dmul_rn(w11, wz0); s.w111 = __dmul_rn(w11, dz);
+  s.r00 = ((int64_t)i0 * N + j0) * N; s.r01 = ((int64_t)i0 * N + j1) * N;
+  s.r10 = ((int64_t)i1 * N + j0) * N; s.r11 = ((int64_t)i1 * N + j1) * N;
+  return s;
+}
+
+template <typename T>
+__device__ __forceinline__ double cic_interp(const T* __restrict__ f, const CicStencil& s) {
+  // same accumulation order as the oracle's trilinear_gather (di, dj, dk lexicographic)
+  double v = s.w000 * (double)__ldg(f + s.r00 + s.k0);
+  v += s.w001 * (double)__ldg(f + s.r00 + s.k1);
+  v += s.w010 * (double)__ldg(f + s.r01 + s.k0);
+  v += s.w011 * (double)__ldg(f + s.r01 + s.k1);
+  v += s.w100 * (double)__ldg(f + s.r10 + s.k0);
+  v += s.w101 * (double)__ldg(f + s.r10 + s.k1);
+  v += s.w110 * (double)__ldg(f + s.r11 + s.k0);
+  v += s.w111 * (double)__ldg(f + s.r11 + s.k1);
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cic_gather_kernel(const T* __restrict__ field, int ncomp, int N, const double* __restrict__ pos, int64_t np,
+                  double cell, double shift, double* __restrict__ out, int accumulate, double scale) {
+  const int64_t n3 = (int64_t)N * N * N;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
+    if (shift != 0.0) { x = __dadd_rn(x, shift); y = __dadd_rn(y, shift); z = __dadd_rn(z, shift); }
+    const CicStencil s = cic_stencil(x, y, z, cell, N);
+    for (int c = 0; c < ncomp; ++c) {
+      const double v = cic_interp(field + c * n3, s) * scale;
+      if (accumulate) out[p * ncomp + c] += v; else out[p * ncomp + c] = v;
+    }
+  }
+}
+
+// pos <- pymod(pos + disp, L)     (`particles += ψ ; particles %= L`)
+__global__ void __launch_bounds__(256)
+displace_wrap_kernel(double* __restrict__ pos, const double* __restrict__ disp, int64_t n3, double L) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride)
+    pos[t] = nb_pymod(__dadd_rn(pos[t], disp[t]), L);
+}
+
+// mom += kick * acc ; pos = pymod(pos + drift * mom, L)
+__global__ void __launch_bounds__(256)
+kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const double* __restrict__ acc, int64_t n3,
+                  double kick, double drift, double L) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride) {
+    const double m = mom[t] + kick * acc[t];
+    mom[t] = m;
+    pos[t] = nb_pymod(pos[t] + drift * m, L);
+  }
+}
+
+// Fused PM tail: gather the 3 force meshes (optionally a second, interlace-shifted set,
+// averaged), kick, drift, wrap.  One pass over the particle stream.
+__global__ void __launch_bounds__(256)
+gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, double cell,
+                         double shift2, double* __restrict__ pos, double* __restrict__ mom,
+                         double* __restrict__ acc_out, int64_t np, double gscale, double kick, double drift,
+                         double L) {
+  const int64_t n3 = (int64_t)N * N * N;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    const double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
+    const CicStencil s = cic_stencil(x, y, z, cell, N);
+    double g[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) g[c] = cic_interp(f1 + c * n3, s);
+    if (f2) {
+      const CicStencil s2 = cic_stencil(__dadd_rn(x, shift2), __dadd_rn(y, shift2), __dadd_rn(z, shift2), cell, N);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) g[c] = 0.5 * (g[c] + cic_interp(f2 + c * n3, s2));
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) g[c] *= gscale;
+    if (acc_out) {
+      acc_out[3 * p] = g[0]; acc_out[3 * p + 1] = g[1]; acc_out[3 * p + 2] = g[2];
+    }
+    if (mom) {
+      const double px[3] = {x, y, z};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const double m = mom[3 * p + c] + kick * g[c];
+        mom[3 * p + c] = m;
+        pos[3 * p + c] = nb_pymod(px[c] + drift * m, L);
+      }
+    }
+  }
+}
+
+extern "C" int nb_cic_gather(nb_ctx* ctx, const void* field, int ncomp, int N, int prec, const double* pos,
+                             int64_t np, double cell, double shift, double scale, int accumulate, double* out,
+                             void* stream) {
+  NB_REQUIRE(ctx && field && out && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(ncomp >= 1 && N >= 1 && cell > 0, "bad ncomp / N / cell");
+  NB_REQUIRE(prec == NB_F32 || prec == NB_F64, "bad prec");
+  if (np == 0) return NB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  const int nblk = nb_grid_for(ctx, np, 256, 16);
+  if (prec == NB_F64)
+    cic_gather_kernel<double><<<nblk, 256, 0, st>>>((const double*)field, ncomp, N, pos, np, cell, shift, out, accumulate, scale);
+  else
+    cic_gather_kernel<float><<<nblk, 256, 0, st>>>((const float*)field, ncomp, N, pos, np, cell, shift, out, accumulate, scale);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+extern "C" int nb_displace_wrap(nb_ctx* ctx, double* pos, const double* disp, int64_t np, double L, void* stream) {
+  NB_REQUIRE(ctx && (np == 0 || (pos && disp)), "NULL argument");
+  NB_REQUIRE(L > 0, "L must be positive");
+  if (np == 0) return NB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  displace_wrap_kernel<<<nb_grid_for(ctx, 3 * np, 256, 16), 256, 0, st>>>(pos, disp, 3 * np, L);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+extern "C" int nb_kick_drift(nb_ctx* ctx, double* pos, double* mom, const double* acc, int64_t np, double kick,
+                             double drift, double L, void* stream) {
+  NB_REQUIRE(ctx && (np == 0 || (pos && mom && acc)), "NULL argument");
+  NB_REQUIRE(L > 0, "L must be positive");
+  if (np == 0) return NB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  kick_drift_kernel<<<nb_grid_for(ctx, 3 * np, 256, 16), 256, 0, st>>>(pos, mom, acc, 3 * np, kick, drift, L);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+extern "C" int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                                    double cell, double* pos, double* mom, double* acc_out, int64_t np,
+                                    double gscale, double kick, double drift, double L, void* stream) {
+  NB_REQUIRE(ctx && force3 && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(N >= 1 && cell > 0 && L > 0, "bad N / cell / L");
+  NB_REQUIRE(mom || acc_out, "nothing to do: give mom (kick+drift) and/or acc_out");
+  if (np == 0) return NB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  gather_kick_drift_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(
+      force3, force3_shifted, N, cell, 0.5 * cell, pos, mom, acc_out, np, gscale, kick, drift, L);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}

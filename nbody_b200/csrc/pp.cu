@@ -1,0 +1,247 @@
+// K4 — PP direct-sum gravity, shared-memory j-tiles, FP32 FMA + rsqrt.
+// No reference source exists for this path (CONCEPT's PP is external); the arithmetic is
+// our softened Newtonian sum   a_i = G Σ_j m_j d / (|d|² + ε²)^{3/2},  d = x_j - x_i,
+// checked against oracle/force.py:pp_accel.
+//
+// Blackwell notes: this is not a dense contraction, so no tensor cores.  The inner loop is
+// 12 FP32-pipe operations + 1 MUFU.RSQ per interaction (20 flop by the usual convention).
+// sm_100a has packed FP32 (FFMA2/FADD2/FMUL2 from PTX fma/add/mul.f32x2): two i-particles
+// ride in one 64-bit register pair, so one interaction costs 6 issue slots on the FMA pipe
+// plus the MUFU.  Both the scalar and the packed loop are kept (template) — bench.py reports
+// which one the build uses and tools/kbench.py times both.
+//
+// Accuracy: FP32 inside a j-tile (512 terms), tile partial sums are folded into FP64
+// accumulators (3 DADD per tile per i-particle — free at this arithmetic intensity).
+#include "common.cuh"
+
+#define PP_THREADS 256
+#define PP_TJ 512
+
+__device__ __forceinline__ float rsqrt_approx(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// pos (Np,3) f64 -> float4 (x - ox, y - oy, z - oz, w)
+__global__ void __launch_bounds__(256)
+pp_pack_kernel(const double* __restrict__ pos, int64_t np, double ox, double oy, double oz, float w,
+               const double* __restrict__ masses, float4* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    out[p] = make_float4((float)(pos[3 * p] - ox), (float)(pos[3 * p + 1] - oy), (float)(pos[3 * p + 2] - oz),
+                         masses ? (float)masses[p] : w);
+  }
+}
+
+template <int IPT, bool PACKED, bool PERIODIC, bool GUARD>
+__global__ void __launch_bounds__(PP_THREADS)
+pp_accel_kernel(const float4* __restrict__ ipos, int64_t ni, const float4* __restrict__ jpos, int64_t nj,
+                int64_t j_chunk, float eps2, float box, float inv_box, double scale, double* __restrict__ acc) {
+  __shared__ float4 tile[PP_TJ];
+  const int64_t ibase = (int64_t)blockIdx.x * (PP_THREADS * IPT) + threadIdx.x;
+  const int64_t j0 = (int64_t)blockIdx.y * j_chunk;
+  const int64_t j1 = (j0 + j_chunk < nj) ? j0 + j_chunk : nj;
+
+  float nxi[IPT], nyi[IPT], nzi[IPT];   // negated i coordinates: d = x_j + (-x_i)
+  double ax64[IPT], ay64[IPT], az64[IPT];
+#pragma unroll
+  for (int q = 0; q < IPT; ++q) {
+    int64_t i = ibase + (int64_t)q * PP_THREADS;
+    if (i >= ni) i = ni - 1;
+    const float4 p = ipos[i];
+    nxi[q] = -p.x; nyi[q] = -p.y; nzi[q] = -p.z;
+    ax64[q] = ay64[q] = az64[q] = 0.0;
+  }
+  // GUARD (eps == 0): coincident points (the self term) contribute nothing instead of NaN
+
+  for (int64_t jt = j0; jt < j1; jt += PP_TJ) {
+    __syncthreads();
+#pragma unroll
+    for (int t = threadIdx.x; t < PP_TJ; t += PP_THREADS) {
+      const int64_t j = jt + t;
+      tile[t] = (j < j1) ? jpos[j] : make_float4(0.f, 0.f, 0.f, 0.f);   // zero mass: no contribution
+    }
+    __syncthreads();
+
+    if constexpr (!PACKED) {
+      float ax[IPT], ay[IPT], az[IPT];
+#pragma unroll
+      for (int q = 0; q < IPT; ++q) ax[q] = ay[q] = az[q] = 0.f;
+#pragma unroll 4
+      for (int t = 0; t < PP_TJ; ++t) {
+        const float4 pj = tile[t];
+#pragma unroll
+        for (int q = 0; q < IPT; ++q) {
+          float dx = pj.x + nxi[q], dy = pj.y + nyi[q], dz = pj.z + nzi[q];
+          if constexpr (PERIODIC) {
+            dx = fmaf(-box, rintf(dx * inv_box), dx);
+            dy = fmaf(-box, rintf(dy * inv_box), dy);
+            dz = fmaf(-box, rintf(dz * inv_box), dz);
+          }
+          float r2 = fmaf(dx, dx, eps2);
+          r2 = fmaf(dy, dy, r2);
+          r2 = fmaf(dz, dz, r2);
+          const float rinv = rsqrt_approx(r2);
+          float s = (pj.w * rinv) * (rinv * rinv);
+          if constexpr (GUARD) s = (r2 > 0.f) ? s : 0.f;
+          ax[q] = fmaf(s, dx, ax[q]);
+          ay[q] = fmaf(s, dy, ay[q]);
+          az[q] = fmaf(s, dz, az[q]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < IPT; ++q) {
+        ax64[q] += (double)ax[q]; ay64[q] += (double)ay[q]; az64[q] += (double)az[q];
+      }
+    } else {
+      constexpr int H = IPT / 2;
+      f32x2 nx2[H], ny2[H], nz2[H], ax2[H], ay2[H], az2[H];
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        nx2[h] = pack2(nxi[2 * h], nxi[2 * h + 1]);
+        ny2[h] = pack2(nyi[2 * h], nyi[2 * h + 1]);
+        nz2[h] = pack2(nzi[2 * h], nzi[2 * h + 1]);
+        ax2[h] = ay2[h] = az2[h] = pack2(0.f, 0.f);
+      }
+      const f32x2 eps22 = pack2(eps2, eps2);
+#pragma unroll 4
+      for (int t = 0; t < PP_TJ; ++t) {
+        const float4 pj = tile[t];
+        const f32x2 xj = pack2(pj.x, pj.x), yj = pack2(pj.y, pj.y), zj = pack2(pj.z, pj.z), wj = pack2(pj.w, pj.w);
+#pragma unroll
+        for (int h = 0; h < H; ++h) {
+          f32x2 dx = add2(xj, nx2[h]), dy = add2(yj, ny2[h]), dz = add2(zj, nz2[h]);
+          if constexpr (PERIODIC) {
+            float a, b;
+            unpack2(dx, a, b); dx = pack2(fmaf(-box, rintf(a * inv_box), a), fmaf(-box, rintf(b * inv_box), b));
+            unpack2(dy, a, b); dy = pack2(fmaf(-box, rintf(a * inv_box), a), fmaf(-box, rintf(b * inv_box), b));
+            unpack2(dz, a, b); dz = pack2(fmaf(-box, rintf(a * inv_box), a), fmaf(-box, rintf(b * inv_box), b));
+          }
+          f32x2 r2 = fma2(dx, dx, eps22);
+          r2 = fma2(dy, dy, r2);
+          r2 = fma2(dz, dz, r2);
+          float r2a, r2b;
+          unpack2(r2, r2a, r2b);
+          const f32x2 rinv = pack2(rsqrt_approx(r2a), rsqrt_approx(r2b));
+          f32x2 s = mul2(mul2(wj, rinv), mul2(rinv, rinv));
+          if constexpr (GUARD) {
+            float sa, sb;
+            unpack2(s, sa, sb);
+            s = pack2(r2a > 0.f ? sa : 0.f, r2b > 0.f ? sb : 0.f);
+          }
+          ax2[h] = fma2(s, dx, ax2[h]);
+          ay2[h] = fma2(s, dy, ay2[h]);
+          az2[h] = fma2(s, dz, az2[h]);
+        }
+      }
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        float a, b;
+        unpack2(ax2[h], a, b); ax64[2 * h] += (double)a; ax64[2 * h + 1] += (double)b;
+        unpack2(ay2[h], a, b); ay64[2 * h] += (double)a; ay64[2 * h + 1] += (double)b;
+        unpack2(az2[h], a, b); az64[2 * h] += (double)a; az64[2 * h + 1] += (double)b;
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < IPT; ++q) {
+    const int64_t i = ibase + (int64_t)q * PP_THREADS;
+    if (i < ni) {
+      atomicAdd(&acc[3 * i + 0], ax64[q] * scale);
+      atomicAdd(&acc[3 * i + 1], ay64[q] * scale);
+      atomicAdd(&acc[3 * i + 2], az64[q] * scale);
+    }
+  }
+}
+
+extern "C" int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy, double oz,
+                          double mass, const double* masses, void* out_xyzw, void* stream) {
+  NB_REQUIRE(ctx && out_xyzw && (np == 0 || pos), "NULL argument");
+  if (np == 0) return NB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  pp_pack_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(pos, np, ox, oy, oz, (float)mass, masses,
+                                                               (float4*)out_xyzw);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+template <int IPT, bool PACKED>
+static int pp_launch(nb_ctx* ctx, const float4* ipos, int64_t ni, const float4* jpos, int64_t nj, float eps2,
+                     float box, double scale, double* acc, cudaStream_t st) {
+  const int64_t per_block = (int64_t)PP_THREADS * IPT;
+  const int64_t nbi = (ni + per_block - 1) / per_block;
+  // split j so that the grid has several waves of CTAs even for small i-shards
+  int64_t jsplit = 1;
+  const int64_t want = (int64_t)ctx->num_sms * 6;
+  if (nbi < want) jsplit = (want + nbi - 1) / nbi;
+  int64_t max_split = (nj + 4 * PP_TJ - 1) / (4 * PP_TJ);
+  if (max_split < 1) max_split = 1;
+  if (jsplit > max_split) jsplit = max_split;
+  if (jsplit > 65535) jsplit = 65535;
+  int64_t j_chunk = (nj + jsplit - 1) / jsplit;
+  j_chunk = ((j_chunk + PP_TJ - 1) / PP_TJ) * PP_TJ;
+  jsplit = (nj + j_chunk - 1) / j_chunk;
+  dim3 grid((unsigned)nbi, (unsigned)jsplit);
+  const float ib = box > 0.f ? 1.f / box : 0.f;
+  if (box > 0.f) {
+    if (eps2 > 0.f)
+      pp_accel_kernel<IPT, PACKED, true, false><<<grid, PP_THREADS, 0, st>>>(ipos, ni, jpos, nj, j_chunk, eps2, box, ib, scale, acc);
+    else
+      pp_accel_kernel<IPT, PACKED, true, true><<<grid, PP_THREADS, 0, st>>>(ipos, ni, jpos, nj, j_chunk, eps2, box, ib, scale, acc);
+  } else {
+    if (eps2 > 0.f)
+      pp_accel_kernel<IPT, PACKED, false, false><<<grid, PP_THREADS, 0, st>>>(ipos, ni, jpos, nj, j_chunk, eps2, box, ib, scale, acc);
+    else
+      pp_accel_kernel<IPT, PACKED, false, true><<<grid, PP_THREADS, 0, st>>>(ipos, ni, jpos, nj, j_chunk, eps2, box, ib, scale, acc);
+  }
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+extern "C" int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
+                           double eps, double box, double scale, int variant, int accumulate, double* acc,
+                           void* stream) {
+  NB_REQUIRE(ctx && acc && (ni == 0 || ipos_xyzw) && (nj == 0 || jpos_xyzw), "NULL argument");
+  NB_REQUIRE(eps >= 0 && box >= 0, "eps and box must be >= 0");
+  NB_REQUIRE(variant >= 0 && variant <= 3, "variant: 0 default, 1 scalar x4, 2 packed x4, 3 packed x8");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  if (!accumulate && ni > 0) NB_CHECK_CUDA(cudaMemsetAsync(acc, 0, sizeof(double) * 3 * ni, st));
+  if (ni == 0 || nj == 0) return NB_OK;
+  const float4* ip = (const float4*)ipos_xyzw;
+  const float4* jp = (const float4*)jpos_xyzw;
+  const float eps2 = (float)(eps * eps);
+  if (variant == 0) variant = 2;
+  switch (variant) {
+    case 1: return pp_launch<4, false>(ctx, ip, ni, jp, nj, eps2, (float)box, scale, acc, st);
+    case 2: return pp_launch<4, true>(ctx, ip, ni, jp, nj, eps2, (float)box, scale, acc, st);
+    default: return pp_launch<8, true>(ctx, ip, ni, jp, nj, eps2, (float)box, scale, acc, st);
+  }
+}

@@ -1,0 +1,89 @@
+// Cell sort for the P3M short-range force (CONCEPT's "Reordering matter particles in memory
+// according to the gravity tiling", log lines 89-90 of the reference's run logs): counting
+// sort of the particles into ncs³ cubic cells of side L/ncs >= r_cut.
+//
+// Output layout (device):
+//   sorted_xyzw[slot] = (x - cx*cs, y - cy*cs, z - cz*cs, mass) in float32 — CELL-RELATIVE
+//                       coordinates (computed in float64, then rounded), so pair separations
+//                       keep ~1e-7·cs absolute accuracy independent of the box size;
+//   perm[slot]        = original particle index;
+//   cell_start[c]     = first slot of cell c = (cx*ncs + cy)*ncs + cz ; cell_start[ncs³] = Np.
+#include <cub/device/device_scan.cuh>
+
+#include "common.cuh"
+
+__device__ __forceinline__ int sort_cell_coord(double x, double L, double inv_cs, int ncs, double* rel, double cs) {
+  double xw = x;
+  if (xw < 0.0 || xw >= L) xw = nb_pymod(xw, L);
+  int c = (int)(xw * inv_cs);
+  if (c >= ncs) c = ncs - 1;
+  if (c < 0) c = 0;
+  *rel = xw - (double)c * cs;
+  return c;
+}
+
+__global__ void __launch_bounds__(256)
+sort_count_kernel(const double* __restrict__ pos, int64_t np, double L, double cs, double inv_cs, int ncs,
+                  int* __restrict__ cell_of, int* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    double r;
+    const int cx = sort_cell_coord(pos[3 * p], L, inv_cs, ncs, &r, cs);
+    const int cy = sort_cell_coord(pos[3 * p + 1], L, inv_cs, ncs, &r, cs);
+    const int cz = sort_cell_coord(pos[3 * p + 2], L, inv_cs, ncs, &r, cs);
+    const int c = (cx * ncs + cy) * ncs + cz;
+    cell_of[p] = c;
+    atomicAdd(&counts[c], 1);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sort_scatter_kernel(const double* __restrict__ pos, int64_t np, double L, double cs, double inv_cs, int ncs,
+                    float mass, const int* __restrict__ cell_of, const int* __restrict__ cell_start,
+                    int* __restrict__ fill, float4* __restrict__ sorted, int* __restrict__ perm) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    const int c = cell_of[p];
+    const int slot = cell_start[c] + atomicAdd(&fill[c], 1);
+    double rx, ry, rz;
+    sort_cell_coord(pos[3 * p], L, inv_cs, ncs, &rx, cs);
+    sort_cell_coord(pos[3 * p + 1], L, inv_cs, ncs, &ry, cs);
+    sort_cell_coord(pos[3 * p + 2], L, inv_cs, ncs, &rz, cs);
+    sorted[slot] = make_float4((float)rx, (float)ry, (float)rz, mass);
+    perm[slot] = (int)p;
+  }
+}
+
+extern "C" int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
+                            void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream) {
+  NB_REQUIRE(ctx && sorted_xyzw && perm && cell_start && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(ncs >= 1 && (int64_t)ncs * ncs * ncs < ((int64_t)1 << 31) - 2, "bad ncs");
+  NB_REQUIRE(np < ((int64_t)1 << 31), "at most 2^31-1 particles per device");
+  NB_REQUIRE(L > 0, "L must be positive");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  const int64_t nc = (int64_t)ncs * ncs * ncs;
+  void *cell_of = nullptr, *counts = nullptr, *tmp = nullptr;
+  int rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_SORT0, sizeof(int) * (size_t)(np > 0 ? np : 1), &cell_of))) return rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_SORT1, sizeof(int) * (size_t)(nc + 1), &counts))) return rc;
+  size_t tmp_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, (int*)counts, cell_start, (int)(nc + 1), st);
+  if ((rc = nb_scratch(ctx, NB_SCR_SORT2, tmp_bytes + 16, &tmp))) return rc;
+  NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(nc + 1), st));
+  const double cs = L / ncs, inv_cs = (double)ncs / L;
+  const int nblk = nb_grid_for(ctx, np > 0 ? np : 1, 256, 16);
+  if (np > 0) {
+    sort_count_kernel<<<nblk, 256, 0, st>>>(pos, np, L, cs, inv_cs, ncs, (int*)cell_of, (int*)counts);
+    NB_LAUNCHED(ctx);
+  }
+  NB_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, (int*)counts, cell_start, (int)(nc + 1), st));
+  ctx->launches += 2;  // cub scan: upsweep + downsweep
+  if (np > 0) {
+    NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(nc + 1), st));
+    sort_scatter_kernel<<<nblk, 256, 0, st>>>(pos, np, L, cs, inv_cs, ncs, (float)mass, (const int*)cell_of,
+                                             cell_start, (int*)counts, (float4*)sorted_xyzw, perm);
+    NB_LAUNCHED(ctx);
+  }
+  return NB_OK;
+}

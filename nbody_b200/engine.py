@@ -163,6 +163,149 @@ class Engine:
                    "nb_power_spectrum")
         return edges, counts, sums
 
+    # -- K7 ---------------------------------------------------------------------------
+    def hermitian_R(self, c1: torch.Tensor, c2: torch.Tensor, guard: bool) -> torch.Tensor:
+        N = c1.shape[0]
+        out = torch.empty((N, N, N), dtype=torch.complex128, device=self.device)
+        _lib.check(self.lib.nb_hermitian_R(self.ctx, _ptr(c1), _ptr(c2), int(N), int(bool(guard)), _ptr(out),
+                                           self.stream), "nb_hermitian_R")
+        return out
+
+    def grf_synthesize(self, pk_grid: torch.Tensor, c1: torch.Tensor, c2: torch.Tensor, L: float, N: int,
+                       guard: bool, use_fac: bool = True, dtype=torch.float32, want_delta=True, want_psi=False):
+        for t in (pk_grid, c1, c2):
+            if t.dtype != torch.float64 or t.shape != (N, N, N) or not t.is_contiguous():
+                raise ValueError("pk_grid, c1, c2 must be contiguous (N,N,N) float64 tensors")
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        fac = float(np.sqrt(2 * np.pi / L ** 3) * N ** 3) if use_fac else 1.0
+        delta = torch.empty((N, N, N), dtype=dtype, device=self.device) if want_delta else None
+        psi = torch.empty((3, N, N, N), dtype=dtype, device=self.device) if want_psi else None
+        _lib.check(self.lib.nb_grf_synthesize(self.ctx, _ptr(pk_grid), _ptr(c1), _ptr(c2), int(N), _ptr(kv), fac,
+                                              int(bool(guard)), F64 if dtype == torch.float64 else F32,
+                                              _ptr(delta), _ptr(psi), self.stream), "nb_grf_synthesize")
+        return delta, psi
+
+    # -- K3 ---------------------------------------------------------------------------
+    def cic_gather(self, field: torch.Tensor, pos: torch.Tensor, cell: float, N: int, shift: float = 0.0,
+                   scale: float = 1.0, out: torch.Tensor | None = None, accumulate: bool = False) -> torch.Tensor:
+        self._check_pos(pos)
+        if field.dim() == 3:
+            field = field.unsqueeze(0)
+        ncomp = field.shape[0]
+        if field.shape[1:] != (N, N, N) or not field.is_contiguous():
+            raise ValueError("field must be contiguous (ncomp,N,N,N)")
+        if out is None:
+            out = torch.empty((pos.shape[0], ncomp), dtype=torch.float64, device=self.device)
+            accumulate = False
+        _lib.check(self.lib.nb_cic_gather(self.ctx, _ptr(field), int(ncomp), int(N), _prec_of(field), _ptr(pos),
+                                          pos.shape[0], float(cell), float(shift), float(scale),
+                                          int(bool(accumulate)), _ptr(out), self.stream), "nb_cic_gather")
+        return out
+
+    def displace_wrap(self, pos: torch.Tensor, disp: torch.Tensor, L: float) -> torch.Tensor:
+        self._check_pos(pos)
+        self._check_pos(disp)
+        _lib.check(self.lib.nb_displace_wrap(self.ctx, _ptr(pos), _ptr(disp), pos.shape[0], float(L), self.stream),
+                   "nb_displace_wrap")
+        return pos
+
+    def kick_drift(self, pos, mom, acc, kick: float, drift: float, L: float):
+        for t in (pos, mom, acc):
+            self._check_pos(t)
+        _lib.check(self.lib.nb_kick_drift(self.ctx, _ptr(pos), _ptr(mom), _ptr(acc), pos.shape[0], float(kick),
+                                          float(drift), float(L), self.stream), "nb_kick_drift")
+        return pos, mom
+
+    def gather_kick_drift(self, force3, force3_shifted, N, cell, pos, mom, acc_out, gscale, kick, drift, L):
+        self._check_pos(pos)
+        _lib.check(self.lib.nb_gather_kick_drift(self.ctx, _ptr(force3), _ptr(force3_shifted), int(N), float(cell),
+                                                 _ptr(pos), _ptr(mom), _ptr(acc_out), pos.shape[0], float(gscale),
+                                                 float(kick), float(drift), float(L), self.stream),
+                   "nb_gather_kick_drift")
+
+    # -- K2 ---------------------------------------------------------------------------
+    def pm_force_mesh(self, pos: torch.Tensor, L: float, N: int, r_s: float = 0.0, deconv_order: int = 2,
+                      interlace_up: bool = False, interlace_down: bool = False, pref: float = 1.0,
+                      out: torch.Tensor | None = None, out_shifted: torch.Tensor | None = None):
+        """3 (+3) float32 force meshes: deposit -> R2C -> K2 -> C2R."""
+        self._check_pos(pos)
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        s = self.sinc_tab(N, L)
+        if out is None:
+            out = torch.empty((3, N, N, N), dtype=torch.float32, device=self.device)
+        if interlace_down and out_shifted is None:
+            out_shifted = torch.empty((3, N, N, N), dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.nb_pm_force_mesh(self.ctx, _ptr(pos), pos.shape[0], L / N, int(N), _ptr(kv), _ptr(s),
+                                             float(r_s), int(deconv_order), int(bool(interlace_up)),
+                                             int(bool(interlace_down)), float(pref), _ptr(out),
+                                             _ptr(out_shifted) if interlace_down else C.c_void_p(0), self.stream),
+                   "nb_pm_force_mesh")
+        return out, (out_shifted if interlace_down else None)
+
+    def kspace_fused(self, rho1, rho2, L, N, r_s, deconv_order, pref, want_shifted=False):
+        """K2 alone on caller-provided half spectra (complex64 [N][N][N/2+1])."""
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        s = self.sinc_tab(N, L)
+        g = torch.empty((3, N, N, N // 2 + 1), dtype=torch.complex64, device=self.device)
+        h = torch.empty_like(g) if want_shifted else None
+        _lib.check(self.lib.nb_kspace_fused(self.ctx, _ptr(rho1), _ptr(rho2), int(N), _ptr(kv), _ptr(s), float(r_s),
+                                            int(deconv_order), float(pref), _ptr(g), _ptr(h), self.stream),
+                   "nb_kspace_fused")
+        return g, h
+
+    # -- K4 ---------------------------------------------------------------------------
+    def pp_pack(self, pos: torch.Tensor, origin=(0.0, 0.0, 0.0), mass: float = 1.0,
+                masses: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+        self._check_pos(pos)
+        if out is None:
+            out = torch.empty((pos.shape[0], 4), dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.nb_pp_pack(self.ctx, _ptr(pos), pos.shape[0], float(origin[0]), float(origin[1]),
+                                       float(origin[2]), float(mass), _ptr(masses), _ptr(out), self.stream),
+                   "nb_pp_pack")
+        return out
+
+    def pp_accel(self, ipos4: torch.Tensor, jpos4: torch.Tensor, eps: float, box: float = 0.0,
+                 scale: float = 1.0, variant: int = 0, out: torch.Tensor | None = None,
+                 accumulate: bool = False) -> torch.Tensor:
+        for t in (ipos4, jpos4):
+            if t.dtype != torch.float32 or t.dim() != 2 or t.shape[1] != 4 or not t.is_contiguous():
+                raise ValueError("packed positions must be contiguous (n,4) float32")
+        if out is None:
+            out = torch.empty((ipos4.shape[0], 3), dtype=torch.float64, device=self.device)
+            accumulate = False
+        _lib.check(self.lib.nb_pp_accel(self.ctx, _ptr(ipos4), ipos4.shape[0], _ptr(jpos4), jpos4.shape[0],
+                                        float(eps), float(box), float(scale), int(variant),
+                                        int(bool(accumulate)), _ptr(out), self.stream), "nb_pp_accel")
+        return out
+
+    # -- K5 ---------------------------------------------------------------------------
+    def cell_sort(self, pos: torch.Tensor, L: float, ncs: int, mass: float = 1.0):
+        self._check_pos(pos)
+        n = pos.shape[0]
+        sorted4 = torch.empty((n, 4), dtype=torch.float32, device=self.device)
+        perm = torch.empty(n, dtype=torch.int32, device=self.device)
+        cell_start = torch.empty(ncs ** 3 + 1, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.nb_cell_sort(self.ctx, _ptr(pos), n, float(L), int(ncs), float(mass), _ptr(sorted4),
+                                         _ptr(perm), _ptr(cell_start), self.stream), "nb_cell_sort")
+        return sorted4, perm, cell_start
+
+    def p3m_short(self, sorted4, perm, cell_start, L: float, ncs: int, r_s: float, r_cut: float, eps: float,
+                  scale: float, out: torch.Tensor, accumulate: bool = False, cell_lo: int = 0,
+                  cell_hi: int | None = None) -> torch.Tensor:
+        u_max = r_cut / (2 * r_s) * 1.0001
+        key = ("split", round(u_max, 9))
+        if key not in self._tab_cache:
+            self._tab_cache[key] = np.ascontiguousarray(tables.split_poly(u_max, 10), dtype=np.float64)
+        coef = self._tab_cache[key]
+        if cell_hi is None:
+            cell_hi = ncs ** 3
+        _lib.check(self.lib.nb_p3m_short(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm), int(ncs),
+                                         int(cell_lo), int(cell_hi), L / ncs, float(r_cut), float(r_s), float(eps),
+                                         coef.ctypes.data_as(C.c_void_p), int(coef.size), float(u_max),
+                                         float(scale), int(bool(accumulate)), _ptr(out), self.stream),
+                   "nb_p3m_short")
+        return out
+
 
 _default: dict[int, Engine] = {}
 

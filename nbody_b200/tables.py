@@ -60,3 +60,26 @@ def sqrt_thresholds(edges):
     thr = smallest(lambda x: np.sqrt(x) >= e)
     thr_gt = smallest(lambda x: np.sqrt(x) > e)
     return thr, float(thr_gt[-1])
+
+
+def split_poly(u_max, degree=10):
+    """Monomial coefficients (low -> high, in t = 2u²/u_max² - 1) of Q with
+    erfc(u) + 2u/sqrt(pi)·exp(-u²) = 1 - u³·Q(u²): the short-range fraction of the Newtonian
+    force for the P3M split.  Chebyshev interpolation on [0, u_max²]; |error| ~ 1e-8."""
+    import math
+
+    from numpy.polynomial import chebyshev as Ch
+
+    def Q(w):
+        w = np.asarray(w, dtype=np.float64)
+        u = np.sqrt(np.maximum(w, 1e-300))
+        with np.errstate(all="ignore"):
+            from math import pi
+            erf = np.vectorize(math.erf)(u)
+            q = (erf - 2 * u / math.sqrt(pi) * np.exp(-w)) / u ** 3
+        series = 4 / (3 * math.sqrt(math.pi)) * (1 - 3 * w / 5 + 3 * w * w / 14 - w ** 3 / 18)
+        return np.where(w < 1e-3, series, q)
+
+    wmax = u_max * u_max
+    c = Ch.chebinterpolate(lambda t: Q((t + 1) * 0.5 * wmax), degree)
+    return Ch.cheb2poly(c)

@@ -37,24 +37,27 @@ def pm_kernel_tables(N, L, r_s=0.0, deconv_order=2):
     return kv, kgrad, t
 
 
-def pm_accel_mesh(pos, L, N, G=1.0, mass=1.0, r_s=0.0, deconv_order=2, interlace=False):
+def pm_accel_mesh(pos, L, N, G=1.0, mass=1.0, r_s=0.0, deconv_order=2, interlace=False,
+                  interlace_down=False):
     """Long-range acceleration on the mesh, 3 x (N,N,N) float64.
       rho      = mass * cic_density / cell³                        (a1)
       g_k      = 4πG · (i k / k²) · rho_k · exp(-k² r_s²) / W^deconv_order,  g_0 = 0
     (φ_k = -4πG ρ_k / k², g = -∇φ; i·k/k² is the reference's ψ operator.)
     interlace: second deposit of positions shifted by +cell/2 in x,y,z, phase-corrected by
-    exp(+i k·s), averaged (upstream interlacing)."""
+    exp(+i k·s), averaged (upstream interlacing).
+    interlace_down: additionally returns the force sampled on the shifted mesh,
+    g2_k = g_k·exp(-i k·s) (downstream interlacing: gather from both, average)."""
     cell = L / N
     kv, kgrad, t = pm_kernel_tables(N, L, r_s, deconv_order)
     nzh = N // 2 + 1
     rho_k = np.fft.rfftn(restate.cic_density(pos, L, N))
+    m = np.fft.fftfreq(N, d=1.0 / N)                          # signed integer frequencies
+    ph = np.exp(1j * np.pi * m / N)                            # exp(+i k_a cell/2)
+    if N % 2 == 0:
+        ph[N // 2] = 0.0          # Hermitian part of exp(±iπ/2): keeps the combined mesh real
+    phase = ph[:, None, None] * ph[None, :, None] * ph[None, None, :nzh]
     if interlace:
         rho2 = np.fft.rfftn(restate.cic_density(pos + 0.5 * cell, L, N))
-        m = np.fft.fftfreq(N, d=1.0 / N)                      # signed integer frequencies
-        ph = np.exp(1j * np.pi * m / N)                        # exp(+i k_a cell/2)
-        if N % 2 == 0:
-            ph[N // 2] = 0.0      # Hermitian part of exp(±iπ/2): keeps the combined mesh real
-        phase = ph[:, None, None] * ph[None, :, None] * ph[None, None, :nzh]
         rho_k = 0.5 * (rho_k + rho2 * phase)
     k2 = (kv ** 2)[:, None, None] + (kv ** 2)[None, :, None] + (kv ** 2)[None, None, :nzh]
     k2[0, 0, 0] = 1.0
@@ -65,13 +68,40 @@ def pm_accel_mesh(pos, L, N, G=1.0, mass=1.0, r_s=0.0, deconv_order=2, interlace
     gx = np.fft.irfftn(1j * kgrad[:, None, None] * base, s=(N, N, N), axes=(0, 1, 2))
     gy = np.fft.irfftn(1j * kgrad[None, :, None] * base, s=(N, N, N), axes=(0, 1, 2))
     gz = np.fft.irfftn(1j * kgrad[None, None, :nzh] * base, s=(N, N, N), axes=(0, 1, 2))
-    return gx, gy, gz
+    if not interlace_down:
+        return gx, gy, gz
+    b2 = base * np.conj(phase)
+    hx = np.fft.irfftn(1j * kgrad[:, None, None] * b2, s=(N, N, N), axes=(0, 1, 2))
+    hy = np.fft.irfftn(1j * kgrad[None, :, None] * b2, s=(N, N, N), axes=(0, 1, 2))
+    hz = np.fft.irfftn(1j * kgrad[None, None, :nzh] * b2, s=(N, N, N), axes=(0, 1, 2))
+    return (gx, gy, gz), (hx, hy, hz)
 
 
-def pm_accel(pos, L, N, **kw):
-    """Long-range acceleration at the particles: CIC gather (adjoint of the deposit)."""
-    g = pm_accel_mesh(pos, L, N, **kw)
-    return np.column_stack([restate.trilinear_gather(c, pos, L, N) for c in g])
+def pm_accel(pos, L, N, interlace_down=False, **kw):
+    """Long-range acceleration at the particles: CIC gather (adjoint of the deposit); with
+    interlace_down the average of the gathers from the plain and the half-cell-shifted mesh."""
+    if not interlace_down:
+        g = pm_accel_mesh(pos, L, N, **kw)
+        return np.column_stack([restate.trilinear_gather(c, pos, L, N) for c in g])
+    g, h = pm_accel_mesh(pos, L, N, interlace_down=True, **kw)
+    a1 = np.column_stack([restate.trilinear_gather(c, pos, L, N) for c in g])
+    a2 = np.column_stack([restate.trilinear_gather(c, pos + 0.5 * L / N, L, N) for c in h])
+    return 0.5 * (a1 + a2)
+
+
+def accel(cfg, pos, periodic_pp=False, i_subset=None):
+    """Acceleration under a ForceConfig-like object (fields method, boxsize, gridsize, G,
+    mass, eps, r_s, r_cut, interlace, deconv_order) — mirrors nbody_b200.force."""
+    if cfg.method == "pp":
+        return pp_accel(pos, cfg.boxsize, cfg.G, cfg.mass, cfg.eps, periodic_pp, i_subset)
+    a = pm_accel(pos, cfg.boxsize, cfg.gridsize, G=cfg.G, mass=cfg.mass, r_s=cfg.r_s,
+                 deconv_order=cfg.deconv_order, interlace=bool(cfg.interlace[0]),
+                 interlace_down=bool(cfg.interlace[1]))
+    if i_subset is not None:
+        a = a[np.asarray(i_subset)]
+    if cfg.method == "p3m":
+        a = a + p3m_short_accel(pos, cfg.boxsize, cfg.r_s, cfg.r_cut, cfg.G, cfg.mass, cfg.eps, i_subset)
+    return a
 
 
 # ------------------------------------------------------------------------------- pair forces

@@ -1,0 +1,127 @@
+"""GPU parity of the PP / PM / P3M force step against OUR float64 restatement
+(oracle/force.py — parity unpinned: the reference has no source for this path).
+Tolerance (SURVEY §8a'): max|Δg| / rms|g| <= 1e-5 for PP, short range and the mesh force
+(float32 mesh / pair arithmetic, float64 index math and accumulation across tiles)."""
+import numpy as np
+import pytest
+
+from conftest import zeldovich_particles
+from oracle import force as oforce
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def F():
+    from nbody_b200 import force as _f
+    return _f
+
+
+def cfg_for(method, n, N, L, **kw):
+    from nbody_b200.params import ForceConfig
+    return ForceConfig(method=method, npart=n ** 3, boxsize=L, gridsize=N, **kw)
+
+
+def err(a, ref):
+    return np.abs(a - ref).max() / np.sqrt((ref ** 2).mean())
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("periodic", [False, True])
+def test_pp_accel(F, variant, periodic):
+    from nbody_b200.engine import default_engine
+    L, n = 500.0, 12
+    pos = zeldovich_particles(n, L, seed=3)
+    cfg = cfg_for("pp", n, 0, L, G=2.5, mass=3.0)
+    st = F.ForceStepper(cfg, default_engine(), pp_variant=variant)
+    eng = default_engine()
+    a = st.accel(eng.to_device(pos), periodic_pp=periodic).cpu().numpy()
+    ref = oforce.accel(cfg, pos, periodic_pp=periodic)
+    assert err(a, ref) <= TOL
+
+
+def test_pp_unsoftened_self_term_and_ragged_sizes(F):
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    rs = np.random.RandomState(0)
+    for npart in (1, 7, 513, 2049):
+        pos = rs.uniform(0, 100.0, size=(npart, 3))
+        cfg = cfg_for("pp", 1, 0, 100.0, softening_frac=0.0)
+        cfg.npart = npart
+        a = F.ForceStepper(cfg, eng).accel(eng.to_device(pos)).cpu().numpy()
+        ref = oforce.pp_accel(pos, eps=0.0)
+        assert np.isfinite(a).all()
+        if npart > 1:
+            assert err(a, ref) <= 5e-5     # eps = 0: close pairs amplify the float32 position rounding
+        else:
+            assert not a.any()
+
+
+@pytest.mark.parametrize("interlace", [(False, False), (True, False), (True, True)])
+@pytest.mark.parametrize("method", ["pm", "p3m"])
+def test_mesh_and_p3m_accel(F, method, interlace):
+    L, n, N = 1000.0, 16, 32
+    pos = zeldovich_particles(n, L, seed=11)
+    cfg = cfg_for(method, n, N, L, interlace=interlace, deconvolve=(True, True), G=1.0, mass=2.0)
+    a = F.accelerations(cfg, pos)
+    ref = oforce.accel(cfg, pos)
+    assert err(a, ref) <= TOL
+
+
+def test_p3m_short_range_clustered_and_empty_cells(F):
+    """Clustered particles: many empty cells, cells with > 32 particles (several i-chunks)."""
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    L, N = 64.0, 32
+    rs = np.random.RandomState(5)
+    pos = np.vstack([rs.normal(20.0, 1.5, size=(700, 3)), rs.normal(45.0, 3.0, size=(500, 3)),
+                     rs.uniform(0, L, size=(300, 3))]) % L
+    cfg = cfg_for("p3m", 1, N, L)
+    cfg.npart = pos.shape[0]
+    st = F.ForceStepper(cfg, eng)
+    acc = eng.to_device(np.zeros_like(pos))
+    st.short_range(eng.to_device(pos), acc, accumulate=False)
+    ref = oforce.p3m_short_accel(pos, L, cfg.r_s, cfg.r_cut, cfg.G, cfg.mass, cfg.eps)
+    assert err(acc.cpu().numpy(), ref) <= TOL
+
+
+@pytest.mark.parametrize("method", ["pm", "p3m", "pp"])
+def test_force_step_kick_drift(F, method):
+    L, n, N = 500.0, 12, 24
+    pos = zeldovich_particles(n, L, seed=21)
+    rs = np.random.RandomState(1)
+    mom = rs.normal(scale=3.0, size=pos.shape)
+    cfg = cfg_for(method, n, N, L, interlace=(True, True), G=1.0, mass=1.5, a=0.5)
+    p1, m1 = F.force_step(cfg, pos, mom, dt_kick=0.3, dt_drift=0.7)
+    acc = oforce.accel(cfg, pos)
+    pr, mr = oforce.kick_drift(pos, mom, acc, L, mass=cfg.mass, a=cfg.a, dt_kick=0.3, dt_drift=0.7)
+    assert np.abs(m1 - mr).max() <= TOL * np.abs(mr).max()
+    d = np.abs(p1 - pr)
+    d = np.minimum(d, L - d)
+    assert d.max() <= 1e-5 * cfg.cell if N else d.max() <= 1e-6
+    assert (p1 >= 0).all() and (p1 < L).all()
+
+
+def test_param_file_drives_the_step(F):
+    """A CONCEPT .param text in the reference's style selects P3M, mesh, interlace, deconvolve."""
+    from nbody_b200 import params
+    text = '''
+_size = 16
+initial_conditions = {'species': 'matter', 'N': _size**3}
+boxsize = 500*Mpc
+potential_options = {
+    'gridsize': _size,
+    'interlace': {'gravity': {'p3m': (True, True)}},
+    'deconvolve': {'gravity': {'p3m': (True, True)}},
+}
+select_forces = {'matter': {'gravity': 'p3m'}}
+H0 = 67.36*km/(s*Mpc)
+Ωb = 0.02237/h**2
+Ωcdm = 0.12/h**2
+'''
+    cfg = params.force_config(text, mesh=32)
+    assert (cfg.method, cfg.npart, cfg.gridsize, cfg.interlace) == ("p3m", 4096, 32, (True, True))
+    pos = zeldovich_particles(16, 500.0, seed=2)
+    a = F.accelerations(cfg, pos)
+    assert err(a, oforce.accel(cfg, pos)) <= TOL
