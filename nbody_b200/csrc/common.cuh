@@ -82,6 +82,11 @@ int nb_plan_many(nb_ctx* ctx, int rank, const int* n, int batch, cufftType type,
                  const int* inembed, int istride, int idist, const int* onembed, int ostride,
                  int odist, cudaStream_t stream, cufftHandle* out);
 
+// C2R / Z2D into `dst`; if dst is not 16-byte aligned (odd N, component c of a packed
+// 3·N^3 array) the transform goes through scratch and is copied (cuFFT needs aligned I/O).
+int nb_exec_c2r(nb_ctx* ctx, cufftHandle plan, int prec, void* spec, void* dst, size_t real_bytes,
+                cudaStream_t st);
+
 static inline int nb_grid_for(const nb_ctx* ctx, int64_t work_items, int block, int max_waves = 8) {
   int64_t want = (work_items + block - 1) / block;
   int64_t cap = (int64_t)ctx->num_sms * max_waves;

@@ -101,3 +101,19 @@ int nb_plan_many(nb_ctx* ctx, int rank, const int* n, int batch, cufftType type,
   *out = it->second;
   return NB_OK;
 }
+
+int nb_exec_c2r(nb_ctx* ctx, cufftHandle plan, int prec, void* spec, void* dst, size_t real_bytes,
+                cudaStream_t st) {
+  void* out = dst;
+  const bool misaligned = ((uintptr_t)dst & 15u) != 0;
+  if (misaligned) {
+    int rc = nb_scratch(ctx, NB_SCR_REAL1, real_bytes, &out);
+    if (rc) return rc;
+  }
+  if (prec == NB_F64)
+    NB_CHECK_CUFFT(cufftExecZ2D(plan, (cufftDoubleComplex*)spec, (cufftDoubleReal*)out));
+  else
+    NB_CHECK_CUFFT(cufftExecC2R(plan, (cufftComplex*)spec, (cufftReal*)out));
+  if (misaligned) NB_CHECK_CUDA(cudaMemcpyAsync(dst, out, real_bytes, cudaMemcpyDeviceToDevice, st));
+  return NB_OK;
+}

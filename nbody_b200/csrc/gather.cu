@@ -121,10 +121,11 @@ gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__
 extern "C" int nb_cic_gather(nb_ctx* ctx, const void* field, int ncomp, int N, int prec, const double* pos,
                              int64_t np, double cell, double shift, double scale, int accumulate, double* out,
                              void* stream) {
-  NB_REQUIRE(ctx && field && out && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(ctx, "ctx is NULL");
   NB_REQUIRE(ncomp >= 1 && N >= 1 && cell > 0, "bad ncomp / N / cell");
   NB_REQUIRE(prec == NB_F32 || prec == NB_F64, "bad prec");
   if (np == 0) return NB_OK;
+  NB_REQUIRE(field && out && pos, "NULL argument");
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   const int nblk = nb_grid_for(ctx, np, 256, 16);

@@ -135,22 +135,24 @@ extern "C" int nb_grf_synthesize(nb_ctx* ctx, const double* pk_grid, const doubl
                                                      (double2*)spec[3]);
     NB_LAUNCHED(ctx);
     if ((rc = nb_plan3d(ctx, N, CUFFT_Z2D, st, &inv))) return rc;
-    if (delta_out) NB_CHECK_CUFFT(cufftExecZ2D(inv, (cufftDoubleComplex*)spec[0], (cufftDoubleReal*)delta_out));
+    if (delta_out && (rc = nb_exec_c2r(ctx, inv, prec, spec[0], delta_out, (size_t)N * N * N * rb, st))) return rc;
     if (psi_out)
       for (int c = 0; c < 3; ++c)
-        NB_CHECK_CUFFT(cufftExecZ2D(inv, (cufftDoubleComplex*)spec[1 + c],
-                                    (cufftDoubleReal*)((char*)psi_out + (size_t)c * N * N * N * rb)));
+        if ((rc = nb_exec_c2r(ctx, inv, prec, spec[1 + c], (char*)psi_out + (size_t)c * N * N * N * rb,
+                              (size_t)N * N * N * rb, st)))
+          return rc;
   } else {
     grf_kernel<float2, float><<<nblk, 256, 0, st>>>(pk_grid, c1, c2, N, k_vals, fac, guard_selfconj, inv_n3,
                                                    (float2*)spec[0], (float2*)spec[1], (float2*)spec[2],
                                                    (float2*)spec[3]);
     NB_LAUNCHED(ctx);
     if ((rc = nb_plan3d(ctx, N, CUFFT_C2R, st, &inv))) return rc;
-    if (delta_out) NB_CHECK_CUFFT(cufftExecC2R(inv, (cufftComplex*)spec[0], (cufftReal*)delta_out));
+    if (delta_out && (rc = nb_exec_c2r(ctx, inv, prec, spec[0], delta_out, (size_t)N * N * N * rb, st))) return rc;
     if (psi_out)
       for (int c = 0; c < 3; ++c)
-        NB_CHECK_CUFFT(cufftExecC2R(inv, (cufftComplex*)spec[1 + c],
-                                    (cufftReal*)((char*)psi_out + (size_t)c * N * N * N * rb)));
+        if ((rc = nb_exec_c2r(ctx, inv, prec, spec[1 + c], (char*)psi_out + (size_t)c * N * N * N * rb,
+                              (size_t)N * N * N * rb, st)))
+          return rc;
   }
   return NB_OK;
 }

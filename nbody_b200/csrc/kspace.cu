@@ -145,9 +145,12 @@ extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, doub
                             interlace_down ? h : nullptr, stream)))
     return rc;
   for (int c = 0; c < 3; ++c)
-    NB_CHECK_CUFFT(cufftExecC2R(inv, (cufftComplex*)g + c * nspec, force3 + c * n3));
+    if ((rc = nb_exec_c2r(ctx, inv, NB_F32, (cufftComplex*)g + c * nspec, force3 + c * n3, n3 * sizeof(float), st)))
+      return rc;
   if (interlace_down)
     for (int c = 0; c < 3; ++c)
-      NB_CHECK_CUFFT(cufftExecC2R(inv, (cufftComplex*)h + c * nspec, force3_shifted + c * n3));
+      if ((rc = nb_exec_c2r(ctx, inv, NB_F32, (cufftComplex*)h + c * nspec, force3_shifted + c * n3,
+                            n3 * sizeof(float), st)))
+        return rc;
   return NB_OK;
 }

@@ -182,8 +182,9 @@ pp_accel_kernel(const float4* __restrict__ ipos, int64_t ni, const float4* __res
 
 extern "C" int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy, double oz,
                           double mass, const double* masses, void* out_xyzw, void* stream) {
-  NB_REQUIRE(ctx && out_xyzw && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(ctx, "ctx is NULL");
   if (np == 0) return NB_OK;
+  NB_REQUIRE(out_xyzw && pos, "NULL argument");
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   pp_pack_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(pos, np, ox, oy, oz, (float)mass, masses,
@@ -228,7 +229,9 @@ static int pp_launch(nb_ctx* ctx, const float4* ipos, int64_t ni, const float4* 
 extern "C" int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
                            double eps, double box, double scale, int variant, int accumulate, double* acc,
                            void* stream) {
-  NB_REQUIRE(ctx && acc && (ni == 0 || ipos_xyzw) && (nj == 0 || jpos_xyzw), "NULL argument");
+  NB_REQUIRE(ctx, "ctx is NULL");
+  if (ni == 0) return NB_OK;
+  NB_REQUIRE(acc && ipos_xyzw && (nj == 0 || jpos_xyzw), "NULL argument");
   NB_REQUIRE(eps >= 0 && box >= 0, "eps and box must be >= 0");
   NB_REQUIRE(variant >= 0 && variant <= 3, "variant: 0 default, 1 scalar x4, 2 packed x4, 3 packed x8");
   cudaStream_t st = (cudaStream_t)stream;
