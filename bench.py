@@ -1,0 +1,525 @@
+#!/usr/bin/env python
+"""bench.py — one JSON line per run (driver contract in the task description).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload p3m|pm|pp|pk] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one batch of synthetic input:
+  p3m  (default) BASELINE config 5: one P3M kick-drift step, 512^3 particles / 1024^3 mesh
+  pm             BASELINE config 4: one PM step, 256^3 particles / 512^3 mesh
+  pp             BASELINE config 3: one PP kick-drift step, 128^3 particles
+  pk             BASELINE config 2: snapshot P(k), 128^3 particles / 256^3 mesh
+`value` is measured with inputs resident in HBM; `e2e` goes through the numpy-level call with
+pinned HOST buffers (H2D of pos+mom and D2H of the updated pos+mom inside the timed region).
+`--impl reference` times the reference-side CPU path (the oracle port: float64 numpy/scipy +
+C loops, all host threads) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (method, n particles per side, mesh, boxsize, metric, unit)
+    "p3m": ("p3m", 512, 1024, 1000.0, "p3m_particle_steps_per_s", "particle-steps/s"),
+    "pm": ("pm", 256, 512, 1000.0, "pm_particle_steps_per_s", "particle-steps/s"),
+    "pp": ("pp", 128, 0, 500.0, "pp_ginteractions_per_s", "Ginteractions/s"),
+    "pk": ("pk", 128, 256, 1000.0, "pk_particles_per_s", "particles/s"),
+}
+CPU_SAMPLE = {"p3m": (128, 256), "pm": (128, 256), "pp": (64, 0), "pk": (128, 256)}   # bounded CPU samples
+FP32_LANES_PER_SM = 128
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "200"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": max(pw), "samples": len(sm)}
+
+
+def surrogate_pk_torch(k):
+    q = k / 0.02
+    return 2.0e4 * q / (1.0 + q ** 2.2) ** 1.4
+
+
+def zeldovich_on_device(eng, n, L, seed, rms_disp_spacing=1.0):
+    """Synthetic Zel'dovich set in lattice order: the reference's recipe
+    (CiC/3D startbetingelser1.py:62-173) with a surrogate P(k); noise from torch's device RNG,
+    δ_k/ψ synthesis by the library's own K7 kernel, ψ sampled at the lattice nodes."""
+    import torch
+    from nbody_b200 import tables
+    dev = eng.device
+    g = torch.Generator(device=dev).manual_seed(seed)
+    c1 = torch.randn((n, n, n), generator=g, device=dev, dtype=torch.float64) / math.sqrt(2)
+    c2 = torch.randn((n, n, n), generator=g, device=dev, dtype=torch.float64) / math.sqrt(2)
+    kv = torch.from_numpy(tables.k_vals(n, L)).to(dev)
+    k2 = kv * kv
+    km = torch.sqrt((k2[:, None, None] + k2[None, :, None]) + k2[None, None, :])
+    km[0, 0, 0] = 1e-10
+    pk = surrogate_pk_torch(km).contiguous()
+    del km
+    _d, psi = eng.grf_synthesize(pk, c1, c2, L, n, guard=True, dtype=torch.float32, want_delta=False, want_psi=True)
+    del pk, c1, c2
+    disp = psi.reshape(3, -1).t().to(torch.float64)
+    del psi
+    disp *= rms_disp_spacing * (L / n) / disp.std()
+    lat = torch.arange(n, device=dev, dtype=torch.float64) * (L / n)
+    pos = torch.stack(torch.meshgrid(lat, lat, lat, indexing="ij"), -1).reshape(-1, 3).contiguous()
+    eng.displace_wrap(pos, disp.contiguous(), L)
+    del disp
+    torch.cuda.empty_cache()
+    return pos
+
+
+def zeldovich_on_host(n, L, seed, rms_disp_spacing=1.0):
+    """Same recipe in numpy for the CPU baseline samples."""
+    from oracle import restate
+    rs = np.random.RandomState(seed)
+    c1 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    c2 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    R = restate.hermitian_R(c1, c2, guard=True)
+    km = restate.k_mag_grid(n, L)
+    km[0, 0, 0] = 1e-10
+    q = km / 0.02
+    _d, psi = restate.grf_delta_psi(2.0e4 * q / (1.0 + q ** 2.2) ** 1.4, R, L, n)
+    disp = np.column_stack([p.ravel() for p in psi])
+    disp *= rms_disp_spacing * (L / n) / disp.std()
+    pos = restate.lattice(L, n) + disp
+    pos %= L
+    return pos
+
+
+# ------------------------------------------------------------------------------- CPU arm
+def cpu_config(workload, n, N, L):
+    from nbody_b200.params import ForceConfig
+    method = WORKLOADS[workload][0]
+    return ForceConfig(method=method if method != "pk" else "pm", npart=n ** 3, boxsize=L, gridsize=N,
+                       interlace=(True, True), deconvolve=(True, True))
+
+
+def cpu_step_once(workload, cfg, pos, mom, workers):
+    """One step of the reference-side CPU path (oracle port) on host arrays."""
+    from oracle import cpu_step
+    if workload == "pk":
+        return cpu_step.snapshot_pk(pos, cfg.boxsize, cfg.gridsize, workers=workers)
+    if workload == "pp":
+        # direct sum is O(Np^2): time an i-subset against all j and extrapolate (stated in `sample`)
+        from oracle import cport
+        return cport.pp_accel(pos, cfg.G, cfg.mass, cfg.eps, 0.0, 0, min(pos.shape[0], 2048))
+    return cpu_step.step(cfg, pos, mom, 1e-3, 1e-3, workers=workers)
+
+
+def cpu_measure(workload, steps=1, warmup=0):
+    from oracle import cport
+    n, N = CPU_SAMPLE[workload]
+    L = WORKLOADS[workload][3]
+    cfg = cpu_config(workload, n, N, L)
+    pos = zeldovich_on_host(n, L, seed=11)
+    mom = np.zeros_like(pos)
+    cores = os.cpu_count() or 1
+    threads = cport.num_threads()
+    for _ in range(warmup):
+        cpu_step_once(workload, cfg, pos, mom, threads)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step_once(workload, cfg, pos, mom, threads)
+    dt = (time.perf_counter() - t0) / steps
+    np3 = float(n ** 3)
+    if workload == "pp":
+        isub = min(n ** 3, 2048)
+        value = isub * np3 / dt / 1e9
+        sample = f"{n}^3 particles, {isub} i-particles x all j per step (rate is size-independent)"
+    else:
+        value = np3 / dt
+        sample = f"{n}^3 particles / {N}^3 mesh per step (1/{round((WORKLOADS[workload][1] / n) ** 3, 1)} of the workload)"
+    return {"value": value, "unit": WORKLOADS[workload][5], "cores": threads, "host_cores": cores, "kind": "port",
+            "sample": sample, "seconds_per_sample_step": dt,
+            "threads_note": "deposit loop serial like the reference's numba loop; gather, pair loops (OpenMP) and "
+                            "scipy.fft use all threads"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = args.workload
+    method, n, N, L, metric, unit = WORKLOADS[wl]
+    steps = max(1, min(args.steps, 3))
+    cb = cpu_measure(wl, steps=steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": unit, "n_gpus": args.gpus,
+            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": cb["seconds_per_sample_step"] * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(wl, n, N, L),
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(wl, n, N, L):
+    method = WORKLOADS[wl][0]
+    c = {"workload": {"p3m": f"P3M step, {n}^3 particles on a {N}^3 mesh (BASELINE config 5)",
+                      "pm": f"PM step, {n}^3 particles on a {N}^3 mesh (BASELINE config 4)",
+                      "pp": f"PP direct-sum kick-drift step, {n}^3 particles (BASELINE config 3)",
+                      "pk": f"snapshot P(k): {n}^3 particles on a {N}^3 mesh (BASELINE config 2)"}[wl],
+         "particles": n ** 3, "mesh": N, "boxsize": L, "input": "Zel'dovich lattice set, rms displacement 1 spacing",
+         "l2": "inputs larger than L2 (no flush needed)" if n >= 256 else "L2 flushed between timed iterations"}
+    if method in ("pm", "p3m"):
+        c.update(interlace=[True, True], deconvolve=[True, True], differentiation="Fourier")
+    if method == "p3m":
+        c.update(r_s_cells=1.25, r_cut_over_rs=4.5)
+    if method in ("pp", "p3m"):
+        c.update(softening="Plummer, eps = 0.025 L / cbrt(Np)")
+    return c
+
+
+# ------------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from nbody_b200.engine import Engine
+    from nbody_b200.force import ForceStepper
+    from nbody_b200.params import ForceConfig
+
+    wl = args.workload
+    method, n, N, L, metric, unit = WORKLOADS[wl]
+    if args.n:
+        n = args.n
+    if args.mesh:
+        N = args.mesh
+    eng = Engine(local)
+    hbm_peak, peak_src, sm_max_mhz = peaks()
+    fp32_peak_tf = 2.0 * FP32_LANES_PER_SM * eng_num_sms(torch, local) * sm_max_mhz * 1e6 / 1e12
+    np_total = n ** 3
+    dt_kick, dt_drift = 1e-3, 1e-3
+    cfg = ForceConfig(method=method if method != "pk" else "pm", npart=np_total, boxsize=L, gridsize=N,
+                      interlace=(True, True), deconvolve=(True, True))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- inputs (resident) -------------------------------------------------------------
+    if world > 1:
+        from nbody_b200.dist import DistForceStepper, shard_particles
+        pos_all = zeldovich_on_device(eng, n, L, seed=20250611)
+        pos = shard_particles(pos_all, method, L, rank, world)
+        del pos_all
+        torch.cuda.empty_cache()
+        stepper = DistForceStepper(cfg, eng, rank, world)
+    else:
+        pos = zeldovich_on_device(eng, n, L, seed=20250611)
+        stepper = ForceStepper(cfg, eng) if method != "pk" else None
+    mom = torch.zeros_like(pos)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=eng.device) if n < 256 else None
+    phases = {}
+
+    def ev():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def one_step(record=None):
+        """One pass of the hot path on resident data; `record` collects (phase, start, end)."""
+        def mark(name, fn):
+            if record is None:
+                return fn()
+            a = ev(); r = fn(); b = ev()
+            record.append((name, a, b))
+            return r
+        if world > 1:
+            return stepper.step(pos, mom, dt_kick, dt_drift, mark=mark)
+        c = cfg
+        if method == "pk":
+            g = mark("deposit", lambda: eng.cic_deposit(pos, L / N, N))
+            mark("overdensity", lambda: eng.grid_affine(g, a=(L / N) ** 3, b=np_total / L ** 3, c=1.0))
+            return mark("fft+shell_bin", lambda: eng.power_spectrum_bins(g, L, N, 300, norm=L ** 3 / N ** 6))
+        if method == "pp":
+            half = 0.5 * L
+            p4 = mark("pack", lambda: eng.pp_pack(pos, origin=(half, half, half), mass=1.0))
+            acc = stepper._acc_buf(pos.shape[0])
+            mark("pp_accel", lambda: eng.pp_accel(p4, p4, c.eps, scale=c.G * c.mass, out=acc))
+            return mark("kick_drift", lambda: eng.kick_drift(pos, mom, acc, c.mass * dt_kick,
+                                                             dt_drift / (c.mass * c.a ** 2), L))
+        f, fs = mark("pm_mesh(deposit x2, R2C x2, kspace, C2R x6)", lambda: stepper.pm_mesh(pos))
+        if method == "pm":
+            return mark("gather_kick_drift", lambda: eng.gather_kick_drift(
+                f, fs, N, c.cell, pos, mom, None, 1.0, c.mass * dt_kick, dt_drift / (c.mass * c.a ** 2), L))
+        acc = stepper._acc_buf(pos.shape[0])
+        mark("gather", lambda: eng.gather_kick_drift(f, fs, N, c.cell, pos, None, acc, 1.0, 0.0, 0.0, L))
+        srt = mark("cell_sort", lambda: eng.cell_sort(pos, L, stepper.ncs, mass=1.0))
+        mark("p3m_short", lambda: eng.p3m_short(srt[0], srt[1], srt[2], L, stepper.ncs, c.r_s, c.r_cut, c.eps,
+                                                scale=c.G * c.mass, out=acc, accumulate=True))
+        return mark("kick_drift", lambda: eng.kick_drift(pos, mom, acc, c.mass * dt_kick,
+                                                         dt_drift / (c.mass * c.a ** 2), L))
+
+    # ---- warm-up + timed region (device clock, max over ranks) -----------------------------
+    for _ in range(max(args.warmup, 3 if args.warmup >= 3 else args.warmup)):
+        one_step()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = eng.launch_count()
+    eng.profile_read()
+    eng.profile_enable(True)
+    recs = []
+    t_start = ev()
+    step_ms = []
+    for _ in range(args.steps):
+        if flush is not None:
+            flush.zero_()
+        a = ev()
+        one_step(recs)
+        b = ev()
+        step_ms.append((a, b))
+    t_end = ev()
+    barrier()
+    launches = eng.launch_count() - launches0
+    eng.profile_enable(False)
+    clocks = sampler.stop() if rank == 0 else None
+    ms = [a.elapsed_time(b) for a, b in step_ms]
+    total_ms = sum(ms)
+    if world > 1:
+        t = torch.tensor([total_ms], device=eng.device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    for name, a, b in recs:
+        phases.setdefault(name, []).append(a.elapsed_time(b))
+    phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
+    work = float(np_total) ** 2 / 1e9 if method == "pp" else float(np_total)
+    value = work / (ms_per_step * 1e-3)
+
+    line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, n, N, L),
+            "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()}, "gpu_launches": int(launches),
+            "gpu_launches_note": "kernels of libnbody_b200.so only (cuFFT/cub launches are library code)"}
+    line["config"]["parallelism"] = "single GPU" if world == 1 else f"{world} x-slabs (dist.py)"
+
+    # ---- rooflines ------------------------------------------------------------------------
+    if rank == 0 or world == 1:
+        line.update(rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world,
+                              stepper, torch))
+    # ---- end to end through host buffers ----------------------------------------------------
+    if world == 1:
+        line["e2e"] = e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work, unit, L, N,
+                                  np_total)
+    else:
+        line["e2e"] = {"value": None, "unit": unit, "note": "host-buffer path measured at N=1 only"}
+    if rank == 0:
+        line["clocks"] = clocks
+        if world == 1 and not args.no_cpu:
+            del pos, mom
+            torch.cuda.empty_cache()
+            line["cpu_baseline"] = cpu_measure(wl, steps=1)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def eng_num_sms(torch, dev):
+    return torch.cuda.get_device_properties(dev).multi_processor_count
+
+
+# flops per pair (stated in DESIGN.md): PP convention 20 (3 sub, 3 fma, rsqrt, 3 mul, 3 fma);
+# the short-range split adds u²,u (2 mul + rsqrt), t (fma), degree-10 Horner (10 fma),
+# u³Q (mul + fma), ·f (mul): 29 flop  ->  49 per in-range pair.
+PP_FLOP, P3M_FLOP = 20.0, 49.0
+
+
+def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world, stepper, torch):
+    out = {}
+    prof = eng.profile_read()
+    avg = {k: v[0] / v[1] for k, v in prof.items()}
+    np_local = float(pos.shape[0])
+    ng = float(N) ** 3
+    modes = float(N) * N * (N // 2 + 1)
+    hbm = []
+    if "deposit" in avg:
+        b = 24.0 * np_local + 8.0 * ng / world
+        hbm.append({"kernel": "cic_deposit (K1, memset + scatter)", "bound": "hbm", "ms": avg["deposit"],
+                    "achieved": b / avg["deposit"] / 1e6, "alg_bytes": b})
+    if "kspace" in avg:
+        b = (16.0 + 48.0) * modes / world
+        hbm.append({"kernel": "kspace_fused (K2)", "bound": "hbm", "ms": avg["kspace"],
+                    "achieved": b / avg["kspace"] / 1e6, "alg_bytes": b})
+    if "pk_bin" in avg:
+        b = 8.0 * modes
+        hbm.append({"kernel": "pk_shell_bin (K6)", "bound": "hbm", "ms": avg["pk_bin"],
+                    "achieved": b / avg["pk_bin"] / 1e6, "alg_bytes": b})
+    for name in ("gather_kick_drift", "gather"):
+        if name in phase_ms:
+            b = (96.0 if name == "gather_kick_drift" else 48.0) * np_local + 24.0 * ng / world
+            hbm.append({"kernel": f"{name} (K3)", "bound": "hbm", "ms": phase_ms[name],
+                        "achieved": b / phase_ms[name] / 1e6, "alg_bytes": b})
+    if method == "pk" and "deposit" in phase_ms:
+        b = 24.0 * np_local + 8.0 * ng
+        hbm.append({"kernel": "cic_deposit (K1, memset + scatter)", "bound": "hbm", "ms": phase_ms["deposit"],
+                    "achieved": b / phase_ms["deposit"] / 1e6, "alg_bytes": b})
+    for h in hbm:
+        h.update(peak=hbm_peak, unit="GB/s", frac=h["achieved"] / hbm_peak, peak_source=peak_src, traffic=None)
+    fp = None
+    if method == "pp" and "pp_accel" in phase_ms:
+        inter = np_local * float(n) ** 3
+        ach = inter * PP_FLOP / (phase_ms["pp_accel"] * 1e-3) / 1e12
+        fp = {"kernel": "pp_accel (K4, FFMA2 j-tile)", "bound": "fp32", "ms": phase_ms["pp_accel"], "achieved": ach,
+              "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
+              "flop_per_interaction": PP_FLOP, "interactions_per_launch": inter,
+              "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
+    if method == "p3m" and "p3m_short" in phase_ms and world == 1:
+        srt = eng.cell_sort(pos, L, stepper.ncs, mass=1.0)
+        cand, inr = eng.p3m_count_pairs(srt[0], srt[2], L, stepper.ncs, cfg.r_cut)
+        t = phase_ms["p3m_short"] * 1e-3
+        ach = inr * P3M_FLOP / t / 1e12
+        fp = {"kernel": "p3m_short (K5, warp-per-cell)", "bound": "fp32", "ms": phase_ms["p3m_short"],
+              "achieved": ach, "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
+              "flop_per_inrange_pair": P3M_FLOP, "inrange_pairs": inr, "candidate_pairs": cand,
+              "candidate_pairs_per_s": cand / t,
+              "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
+    allk = hbm + ([fp] if fp else [])
+    if allk:
+        dom = max(allk, key=lambda r: r["ms"])
+        out["roofline"] = dom
+        out["rooflines_all"] = allk
+    if prof:
+        out["library_phase_ms"] = {k: round(v[0] / v[1], 4) for k, v in prof.items()}
+    return out
+
+
+def e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work, unit, L, N, np_total):
+    """Same step through HOST buffers: pinned pos/mom -> device, step, updated pos/mom -> pinned
+    host, every step, copies inside the timed region (CUDA events on the launching stream)."""
+    steps = max(1, min(args.steps, 3))
+    if method == "pk":
+        hpos = torch.empty(pos.shape, dtype=torch.float64, pin_memory=True)
+        hpos.copy_(pos)
+        hout = torch.empty(2 * 299, dtype=torch.float64, pin_memory=True)
+        h2d, d2h = hpos.numel() * 8, 299 * 16
+    else:
+        hpos = torch.empty(pos.shape, dtype=torch.float64, pin_memory=True)
+        hmom = torch.empty(pos.shape, dtype=torch.float64, pin_memory=True)
+        hpos.copy_(pos); hmom.copy_(mom)
+        opos = torch.empty(pos.shape, dtype=torch.float64, pin_memory=True)
+        omom = torch.empty(pos.shape, dtype=torch.float64, pin_memory=True)
+        h2d, d2h = 2 * hpos.numel() * 8, 2 * hpos.numel() * 8
+    torch.cuda.synchronize()
+
+    def host_step():
+        pos.copy_(hpos, non_blocking=True)
+        if method != "pk":
+            mom.copy_(hmom, non_blocking=True)
+        r = one_step()
+        if method == "pk":
+            _e, counts, sums = r
+            hout[:299].copy_(counts.to(torch.float64), non_blocking=True)
+            hout[299:].copy_(sums, non_blocking=True)
+        else:
+            opos.copy_(pos, non_blocking=True)
+            omom.copy_(mom, non_blocking=True)
+
+    host_step()
+    torch.cuda.synchronize()
+    a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        host_step()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
+            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+            "api": "nbody_b200.force.ForceStepper.step on pinned host pos/mom (numpy-level force_step path)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="p3m", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=0, help="override particles per side (development only)")
+    ap.add_argument("--mesh", type=int, default=0, help="override mesh size (development only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -52,6 +52,18 @@ int nb_release_scratch(nb_ctx* ctx);
 /* Number of kernels this library has launched through `ctx` since nb_init (bench.py's
  * gpu_launches claim). */
 int64_t nb_launch_count(nb_ctx* ctx);
+/* Optional device-side phase timing of the composite calls (CUDA events on the caller's
+ * stream around each phase).  nb_profile_read sums the recorded intervals per phase id
+ * (NB_PH_*), returns them in HOST arrays and clears the records. */
+#define NB_PH_DEPOSIT 0   /* K1 inside nb_pm_force_mesh (memset + kernel)        */
+#define NB_PH_FFT_FWD 1   /* cuFFT R2C                                          */
+#define NB_PH_KSPACE 2    /* K2                                                 */
+#define NB_PH_FFT_INV 3   /* cuFFT C2R (all components)                         */
+#define NB_PH_PK_BIN 4    /* K6 shell-binning kernel inside nb_power_spectrum   */
+#define NB_PH_SORT 5      /* cell sort                                          */
+#define NB_PH_COUNT 6
+int nb_profile_enable(nb_ctx* ctx, int on);
+int nb_profile_read(nb_ctx* ctx, double* ms_sum_host, int64_t* count_host, int nphases);
 
 /* ---- K1  CIC mass deposit -------------------------------------------------------------
  * Replaces cic_density(positions, boxsize, N)   FraP_kTilDelta.py:93-123,
@@ -198,6 +210,11 @@ int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start
                  int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
                  double eps, const double* coef_host, int ncoef, double u_max, double scale,
                  int accumulate, double* acc, void* stream);
+/* Pair statistics of the same traversal: out2[0] = candidate pairs (all j in the 27
+ * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]). */
+int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, int ncs,
+                       int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, int64_t* out2,
+                       void* stream);
 
 #ifdef __cplusplus
 }

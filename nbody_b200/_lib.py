@@ -23,6 +23,8 @@ PROTOTYPES = {
     "nb_last_error": (C.c_char_p, []),
     "nb_release_scratch": (c_i32, [c_vp]),
     "nb_launch_count": (c_i64, [c_vp]),
+    "nb_profile_enable": (c_i32, [c_vp, c_i32]),
+    "nb_profile_read": (c_i32, [c_vp, c_vp, c_vp, c_i32]),
     "nb_cic_deposit": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i32, c_f64, c_i32, c_vp, c_vp]),
     "nb_grid_sum": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp]),
     "nb_grid_affine": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_f64, c_vp, c_f64, c_f64, c_f64, c_vp]),
@@ -44,6 +46,7 @@ PROTOTYPES = {
     "nb_cell_sort": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
                              c_f64, c_f64, c_i32, c_vp, c_vp]),
+    "nb_p3m_count_pairs": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp]),
 }
 
 

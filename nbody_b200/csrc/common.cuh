@@ -7,6 +7,7 @@
 #include <string.h>
 #include <map>
 #include <tuple>
+#include <vector>
 
 #include "../../include/nbody_b200.h"
 
@@ -71,6 +72,27 @@ struct nb_ctx {
   size_t scratch_bytes[NB_SCR_NSLOTS] = {};
   // key: (cufftType, n0, n1, n2, batch, layout) ; layout 0 = plain 3-D
   std::map<std::tuple<int, int, int, int, int, int>, cufftHandle> plans;
+  // optional per-phase device timing (nb_profile_enable): (phase, start, end) event pairs
+  bool prof_on = false;
+  std::vector<std::tuple<int, cudaEvent_t, cudaEvent_t>> prof_events;
+};
+
+// RAII phase marker: records a CUDA event pair on `st` around a phase of a composite call
+// (deposit / FFT / k-space ... inside nb_pm_force_mesh) when profiling is enabled.
+struct NbPhase {
+  nb_ctx* ctx;
+  cudaStream_t st;
+  cudaEvent_t e1 = nullptr;
+  NbPhase(nb_ctx* c, int phase, cudaStream_t s) : ctx(c), st(s) {
+    if (!ctx->prof_on) return;
+    cudaEvent_t e0;
+    if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { e1 = nullptr; return; }
+    cudaEventRecord(e0, st);
+    ctx->prof_events.emplace_back(phase, e0, e1);
+  }
+  ~NbPhase() {
+    if (e1) cudaEventRecord(e1, st);
+  }
 };
 
 // grow-only scratch

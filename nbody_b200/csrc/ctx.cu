@@ -117,3 +117,31 @@ int nb_exec_c2r(nb_ctx* ctx, cufftHandle plan, int prec, void* spec, void* dst, 
   if (misaligned) NB_CHECK_CUDA(cudaMemcpyAsync(dst, out, real_bytes, cudaMemcpyDeviceToDevice, st));
   return NB_OK;
 }
+
+extern "C" int nb_profile_enable(nb_ctx* ctx, int on) {
+  NB_REQUIRE(ctx != nullptr, "ctx is NULL");
+  ctx->prof_on = on != 0;
+  return NB_OK;
+}
+
+// Sums the recorded phase durations: ms_sum_host[phase] (milliseconds) and
+// count_host[phase] (number of recorded intervals) for phase < nphases; clears the records.
+extern "C" int nb_profile_read(nb_ctx* ctx, double* ms_sum_host, int64_t* count_host, int nphases) {
+  NB_REQUIRE(ctx && ms_sum_host && count_host && nphases > 0, "bad arguments");
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  for (int p = 0; p < nphases; ++p) { ms_sum_host[p] = 0.0; count_host[p] = 0; }
+  for (auto& t : ctx->prof_events) {
+    const int ph = std::get<0>(t);
+    cudaEvent_t e0 = std::get<1>(t), e1 = std::get<2>(t);
+    float ms = 0.f;
+    if (cudaEventSynchronize(e1) == cudaSuccess && cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess &&
+        ph >= 0 && ph < nphases) {
+      ms_sum_host[ph] += ms;
+      count_host[ph] += 1;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+  }
+  ctx->prof_events.clear();
+  return NB_OK;
+}

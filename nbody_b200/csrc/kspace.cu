@@ -135,15 +135,29 @@ extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, doub
   cufftHandle fwd, inv;
   if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
   if ((rc = nb_plan3d(ctx, N, CUFFT_C2R, st, &inv))) return rc;
-  if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.0, 0, nullptr, stream))) return rc;
-  NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)rho, (cufftComplex*)s1));
+  {
+    NbPhase ph(ctx, NB_PH_DEPOSIT, st);
+    if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.0, 0, nullptr, stream))) return rc;
+  }
+  {
+    NbPhase ph(ctx, NB_PH_FFT_FWD, st);
+    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)rho, (cufftComplex*)s1));
+  }
   if (interlace_up) {
-    if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.5 * cell, 0, nullptr, stream))) return rc;
+    {
+      NbPhase ph(ctx, NB_PH_DEPOSIT, st);
+      if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.5 * cell, 0, nullptr, stream))) return rc;
+    }
+    NbPhase ph(ctx, NB_PH_FFT_FWD, st);
     NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)rho, (cufftComplex*)s2));
   }
-  if ((rc = nb_kspace_fused(ctx, s1, interlace_up ? s2 : nullptr, N, k_vals, sinc_tab, r_s, deconv_order, pref, g,
-                            interlace_down ? h : nullptr, stream)))
-    return rc;
+  {
+    NbPhase ph(ctx, NB_PH_KSPACE, st);
+    if ((rc = nb_kspace_fused(ctx, s1, interlace_up ? s2 : nullptr, N, k_vals, sinc_tab, r_s, deconv_order, pref, g,
+                              interlace_down ? h : nullptr, stream)))
+      return rc;
+  }
+  NbPhase ph_inv(ctx, NB_PH_FFT_INV, st);
   for (int c = 0; c < 3; ++c)
     if ((rc = nb_exec_c2r(ctx, inv, NB_F32, (cufftComplex*)g + c * nspec, force3 + c * n3, n3 * sizeof(float), st)))
       return rc;

@@ -141,3 +141,63 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   NB_LAUNCHED(ctx);
   return NB_OK;
 }
+
+// Pair statistics of the same traversal (not timed; bench.py uses it to convert the kernel
+// time into candidate-pair and in-range-pair rates): out[0] = candidate pairs, out[1] = pairs
+// with 0 < r < r_cut.
+__global__ void __launch_bounds__(P3M_WARPS * 32)
+p3m_count_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start, int ncs, int64_t cell_lo,
+                 int64_t cell_hi, float cs, float rc2, unsigned long long* __restrict__ out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t wstride = (int64_t)gridDim.x * P3M_WARPS;
+  unsigned long long cand = 0, inr = 0;
+  for (int64_t c = cell_lo + (int64_t)blockIdx.x * P3M_WARPS + warp; c < cell_hi; c += wstride) {
+    const int is = cell_start[c], ie = cell_start[c + 1];
+    if (is == ie) continue;
+    const int cz = (int)(c % ncs), cy = (int)((c / ncs) % ncs), cx = (int)(c / ((int64_t)ncs * ncs));
+    for (int i = is + lane; i < ie; i += 32) {
+      const float4 pi = sorted[i];
+      for (int ox = -1; ox <= 1; ++ox)
+        for (int oy = -1; oy <= 1; ++oy)
+          for (int oz = -1; oz <= 1; ++oz) {
+            const int nx = (cx + ox + ncs) % ncs, ny = (cy + oy + ncs) % ncs, nz = (cz + oz + ncs) % ncs;
+            const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+            const int js = cell_start[n], je = cell_start[n + 1];
+            cand += (unsigned long long)(je - js);
+            for (int j = js; j < je; ++j) {
+              const float4 pj = sorted[j];
+              const float dx = pj.x + ox * cs - pi.x, dy = pj.y + oy * cs - pi.y, dz = pj.z + oz * cs - pi.z;
+              const float r2 = dx * dx + dy * dy + dz * dz;
+              inr += (r2 < rc2 && r2 > 0.f) ? 1ull : 0ull;
+            }
+          }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    cand += __shfl_xor_sync(0xffffffffu, cand, o);
+    inr += __shfl_xor_sync(0xffffffffu, inr, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&out[0], cand);
+    atomicAdd(&out[1], inr);
+  }
+}
+
+extern "C" int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, int ncs,
+                                  int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
+                                  int64_t* out2, void* stream) {
+  NB_REQUIRE(ctx && sorted_xyzw && cell_start && out2, "NULL argument");
+  NB_REQUIRE(ncs >= 3 && cell_lo >= 0 && cell_lo <= cell_hi && cell_hi <= (int64_t)ncs * ncs * ncs, "bad cells");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  NB_CHECK_CUDA(cudaMemsetAsync(out2, 0, 2 * sizeof(int64_t), st));
+  if (cell_lo == cell_hi) return NB_OK;
+  int64_t nblk = (cell_hi - cell_lo + P3M_WARPS - 1) / P3M_WARPS;
+  const int64_t cap = (int64_t)ctx->num_sms * 64;
+  if (nblk > cap) nblk = cap;
+  p3m_count_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start, ncs, cell_lo, cell_hi,
+                                                         (float)cell_side, (float)(r_cut * r_cut),
+                                                         (unsigned long long*)out2);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}

@@ -183,16 +183,20 @@ extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec
   int rc = nb_scratch(ctx, NB_SCR_SPEC0, (size_t)nspec * (prec == NB_F64 ? 16 : 8), &spec);
   if (rc) return rc;
   cufftHandle fwd;
-  if (prec == NB_F64) {
-    if ((rc = nb_plan3d(ctx, N, CUFFT_D2Z, st, &fwd))) return rc;
-    NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)const_cast<void*>(delta), (cufftDoubleComplex*)spec));
-  } else {
-    if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
-    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)const_cast<void*>(delta), (cufftComplex*)spec));
+  {
+    NbPhase phf(ctx, NB_PH_FFT_FWD, st);
+    if (prec == NB_F64) {
+      if ((rc = nb_plan3d(ctx, N, CUFFT_D2Z, st, &fwd))) return rc;
+      NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)const_cast<void*>(delta), (cufftDoubleComplex*)spec));
+    } else {
+      if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
+      NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)const_cast<void*>(delta), (cufftComplex*)spec));
+    }
   }
   NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * (n_edges - 1), st));
   NB_CHECK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * (n_edges - 1), st));
   NB_REQUIRE(thresh_first > 0 && thresh_last > thresh_first, "bin thresholds must be positive and increasing");
+  NbPhase ph(ctx, NB_PH_PK_BIN, st);
   return nb_pk_bin_spectrum(ctx, spec, N, prec, k2_tab, sinc_tab, thresh, thresh_hi, n_edges, window_power,
                             clip_mode, clip_val, norm, closed_last, thresh_first, thresh_last, counts, sums, st);
 }

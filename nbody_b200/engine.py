@@ -63,6 +63,19 @@ class Engine:
     def launch_count(self) -> int:
         return int(self.lib.nb_launch_count(self.ctx))
 
+    PHASES = ("deposit", "fft_fwd", "kspace", "fft_inv", "pk_bin", "sort")
+
+    def profile_enable(self, on: bool = True):
+        _lib.check(self.lib.nb_profile_enable(self.ctx, int(bool(on))), "nb_profile_enable")
+
+    def profile_read(self) -> dict:
+        """{phase: (total ms, intervals)} recorded since the last read (device-side CUDA events)."""
+        n = len(self.PHASES)
+        ms = (C.c_double * n)()
+        cnt = (C.c_int64 * n)()
+        _lib.check(self.lib.nb_profile_read(self.ctx, ms, cnt, n), "nb_profile_read")
+        return {self.PHASES[i]: (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}
+
     def release_scratch(self):
         _lib.check(self.lib.nb_release_scratch(self.ctx), "nb_release_scratch")
 
@@ -305,6 +318,14 @@ class Engine:
                                          float(scale), int(bool(accumulate)), _ptr(out), self.stream),
                    "nb_p3m_short")
         return out
+
+    def p3m_count_pairs(self, sorted4, cell_start, L: float, ncs: int, r_cut: float, cell_lo=0, cell_hi=None):
+        out = torch.empty(2, dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.nb_p3m_count_pairs(self.ctx, _ptr(sorted4), _ptr(cell_start), int(ncs), int(cell_lo),
+                                               int(ncs ** 3 if cell_hi is None else cell_hi), L / ncs,
+                                               float(r_cut), _ptr(out), self.stream), "nb_p3m_count_pairs")
+        c = out.cpu().numpy()
+        return int(c[0]), int(c[1])
 
 
 _default: dict[int, Engine] = {}
