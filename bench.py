@@ -275,14 +275,19 @@ def run_ours(args):
     if world > 1:
         from nbody_b200.dist import DistForceStepper, shard_particles
         pos_all = zeldovich_on_device(eng, n, L, seed=20250611)
-        pos = shard_particles(pos_all, method, L, rank, world)
+        pos = shard_particles(pos_all, method, L, rank, world, N)
         del pos_all
         torch.cuda.empty_cache()
-        stepper = DistForceStepper(cfg, eng, rank, world)
+        if method == "pk":
+            from nbody_b200.dist import DistPowerSpectrum, TorchComm
+            stepper = DistPowerSpectrum(eng, TorchComm(), N, L)
+        else:
+            stepper = DistForceStepper(cfg, eng, rank, world)
     else:
         pos = zeldovich_on_device(eng, n, L, seed=20250611)
         stepper = ForceStepper(cfg, eng) if method != "pk" else None
-    mom = torch.zeros_like(pos)
+    state = {"pos": pos, "mom": torch.zeros_like(pos)}
+    mom = state["mom"]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=eng.device) if n < 256 else None
     phases = {}
 
@@ -300,7 +305,12 @@ def run_ours(args):
             record.append((name, a, b))
             return r
         if world > 1:
-            return stepper.step(pos, mom, dt_kick, dt_drift, mark=mark)
+            if method == "pk":
+                return stepper(state["pos"], np_total, mark=mark)
+            # migration may hand back new tensors: the particle set of this rank is `state`
+            state["pos"], state["mom"] = stepper.step(state["pos"], state["mom"], dt_kick, dt_drift, mark=mark,
+                                                      n_total=np_total)
+            return None
         c = cfg
         if method == "pk":
             g = mark("deposit", lambda: eng.cic_deposit(pos, L / N, N))
@@ -368,18 +378,19 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, n, N, L),
             "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()}, "gpu_launches": int(launches),
             "gpu_launches_note": "kernels of libnbody_b200.so only (cuFFT/cub launches are library code)"}
-    line["config"]["parallelism"] = "single GPU" if world == 1 else f"{world} x-slabs (dist.py)"
+    line["config"]["parallelism"] = ("single GPU" if world == 1 else
+                                     f"{world} ranks, i-sharded + all-gather of j" if method == "pp" else
+                                     f"{world} x-slabs: slab FFT all-to-all, ghost planes, halo particles")
 
     # ---- rooflines ------------------------------------------------------------------------
-    if rank == 0 or world == 1:
-        line.update(rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world,
-                              stepper, torch))
+    line.update(rooflines(eng, method, cfg, state["pos"], phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world,
+                          stepper, torch))
     # ---- end to end through host buffers ----------------------------------------------------
     if world == 1:
         line["e2e"] = e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work, unit, L, N,
                                   np_total)
     else:
-        line["e2e"] = {"value": None, "unit": unit, "note": "host-buffer path measured at N=1 only"}
+        line["e2e"] = e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier)
     if rank == 0:
         line["clocks"] = clocks
         if world == 1 and not args.no_cpu:
@@ -402,9 +413,15 @@ PP_FLOP, P3M_FLOP = 20.0, 49.0
 
 
 def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world, stepper, torch):
+    """Per-kernel rooflines of THIS rank (rank 0's are printed): algorithmic bytes / flops of the
+    rank's share of the work over the kernel's CUDA-event duration."""
     out = {}
     prof = eng.profile_read()
     avg = {k: v[0] / v[1] for k, v in prof.items()}
+    if world > 1 and "kspace" in phase_ms:
+        avg["kspace"] = phase_ms["kspace"]      # pure kernel phases of dist.DistForceStepper
+    if world > 1 and "shell_bin" in phase_ms:
+        avg["pk_bin"] = phase_ms["shell_bin"]
     np_local = float(pos.shape[0])
     ng = float(N) ** 3
     modes = float(N) * N * (N // 2 + 1)
@@ -418,7 +435,7 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
         hbm.append({"kernel": "kspace_fused (K2)", "bound": "hbm", "ms": avg["kspace"],
                     "achieved": b / avg["kspace"] / 1e6, "alg_bytes": b})
     if "pk_bin" in avg:
-        b = 8.0 * modes
+        b = 8.0 * modes / world
         hbm.append({"kernel": "pk_shell_bin (K6)", "bound": "hbm", "ms": avg["pk_bin"],
                     "achieved": b / avg["pk_bin"] / 1e6, "alg_bytes": b})
     for name in ("gather_kick_drift", "gather"):
@@ -434,15 +451,21 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
         h.update(peak=hbm_peak, unit="GB/s", frac=h["achieved"] / hbm_peak, peak_source=peak_src, traffic=None)
     fp = None
     if method == "pp" and "pp_accel" in phase_ms:
-        inter = np_local * float(n) ** 3
+        inter = np_local * float(n) ** 3        # this rank's i-particles x all j
         ach = inter * PP_FLOP / (phase_ms["pp_accel"] * 1e-3) / 1e12
         fp = {"kernel": "pp_accel (K4, FFMA2 j-tile)", "bound": "fp32", "ms": phase_ms["pp_accel"], "achieved": ach,
               "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
               "flop_per_interaction": PP_FLOP, "interactions_per_launch": inter,
               "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
-    if method == "p3m" and "p3m_short" in phase_ms and world == 1:
-        srt = eng.cell_sort(pos, L, stepper.ncs, mass=1.0)
-        cand, inr = eng.p3m_count_pairs(srt[0], srt[2], L, stepper.ncs, cfg.r_cut)
+    if method == "p3m" and "p3m_short" in phase_ms:
+        if world == 1:
+            srt = eng.cell_sort(pos, L, stepper.ncs, mass=1.0)
+            cand, inr = eng.p3m_count_pairs(srt[0], srt[2], L, stepper.ncs, cfg.r_cut)
+        else:   # own + halo set of the last step; halo copies are sources only
+            halo = stepper.halo_exchange(pos)
+            srt = eng.cell_sort(torch.cat([pos, halo]), L, stepper.ncs, mass=1.0)
+            cand, inr = eng.p3m_count_pairs(srt[0], srt[2], L, stepper.ncs, cfg.r_cut, perm=srt[1],
+                                            i_limit=pos.shape[0])
         t = phase_ms["p3m_short"] * 1e-3
         ach = inr * P3M_FLOP / t / 1e12
         fp = {"kernel": "p3m_short (K5, warp-per-cell)", "bound": "fp32", "ms": phase_ms["p3m_short"],
@@ -503,6 +526,60 @@ def e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work
     return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
             "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "api": "nbody_b200.force.ForceStepper.step on pinned host pos/mom (numpy-level force_step path)"}
+
+
+def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier):
+    """N > 1: every rank stages ITS shard through pinned host memory each step (H2D of pos+mom,
+    the sharded step, D2H of the updated shard); device time, max over ranks."""
+    steps = max(1, min(args.steps, 3))
+    pos0 = state["pos"]
+    hpos = torch.empty(pos0.shape, dtype=torch.float64, pin_memory=True)
+    hpos.copy_(pos0)
+    if method == "pk":
+        hout = torch.empty(2 * 299, dtype=torch.float64, pin_memory=True)
+        h2d, d2h = hpos.numel() * 8, 299 * 16
+    else:
+        hmom = torch.empty(pos0.shape, dtype=torch.float64, pin_memory=True)
+        hmom.copy_(state["mom"])
+        cap = int(pos0.shape[0] * 1.05) + 1024            # room for particles that migrate in
+        opos = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+        omom = torch.empty((cap, 3), dtype=torch.float64, pin_memory=True)
+        h2d, d2h = 2 * hpos.numel() * 8, 2 * hpos.numel() * 8
+    dpos, dmom = torch.empty_like(pos0), torch.empty_like(pos0)
+    torch.cuda.synchronize()
+
+    def host_step():
+        dpos.copy_(hpos, non_blocking=True)
+        state["pos"] = dpos
+        if method != "pk":
+            dmom.copy_(hmom, non_blocking=True)
+            state["mom"] = dmom
+        r = one_step()
+        if method == "pk":
+            _e, counts, sums = r
+            hout[:299].copy_(counts.to(torch.float64), non_blocking=True)
+            hout[299:].copy_(sums, non_blocking=True)
+        else:
+            k = min(state["pos"].shape[0], opos.shape[0])
+            opos[:k].copy_(state["pos"][:k], non_blocking=True)
+            omom[:k].copy_(state["mom"][:k], non_blocking=True)
+
+    host_step()
+    barrier()
+    a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        host_step()
+    b.record()
+    barrier()
+    t = torch.tensor([a.elapsed_time(b) / steps], device=eng.device, dtype=torch.float64)
+    bt = torch.tensor([float(h2d), float(d2h)], device=eng.device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(bt)
+    ms = float(t.item())
+    return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
+            "h2d_bytes_per_step": int(bt[0].item()), "d2h_bytes_per_step": int(bt[1].item()),
+            "api": "nbody_b200.dist.DistForceStepper.step, each rank's shard staged through pinned host memory"}
 
 
 def main():

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 1
+#define NB_ABI_VERSION 2
 
 #define NB_OK 0
 #define NB_EINVAL (-1)  /* bad argument */
@@ -203,18 +203,64 @@ int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos
  * (cell-relative x,y,z, mass), perm[slot] = original index, cell_start[ncs^3+1].
  * nb_p3m_short: for the cells [cell_lo, cell_hi) (slab of a multi-GPU run, or all):
  *   acc[perm[i]] (=|+=) scale · Σ_{r<r_cut} w_j d/(r²+eps²)^{3/2}·(1 - u³Q(t)),
- *   u = r/(2 r_s), t = 2u²/u_max² - 1, Q given by ncoef = 11 monomial coefficients (host). */
+ *   u = r/(2 r_s), t = 2u²/u_max² - 1, Q given by ncoef = 11 monomial coefficients (host).
+ * i_limit > 0: particles with perm >= i_limit are sources only (halo copies of another slab's
+ * particles in a multi-GPU run; their acc rows are not touched); 0 = every particle.
+ * sorted_xyzw.w must be the uniform mass nb_cell_sort writes. */
 int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
                  void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream);
 int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
                  int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
                  double eps, const double* coef_host, int ncoef, double u_max, double scale,
-                 int accumulate, double* acc, void* stream);
+                 int accumulate, int64_t i_limit, double* acc, void* stream);
 /* Pair statistics of the same traversal: out2[0] = candidate pairs (all j in the 27
- * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]). */
-int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, int ncs,
-                       int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, int64_t* out2,
-                       void* stream);
+ * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]).
+ * perm / i_limit as in nb_p3m_short (perm may be NULL when i_limit = 0). */
+int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start,
+                       const int32_t* perm, int64_t i_limit, int ncs, int64_t cell_lo, int64_t cell_hi,
+                       double cell_side, double r_cut, int64_t* out2, void* stream);
+
+/* ---- slab decomposition (multi-GPU) ---------------------------------------------
+ * No reference counterpart: every CONCEPT run of the reference is one process ("Domain
+ * decomposition: 1x1x1", run logs line 17).  Real mesh in x-slabs (rank r owns planes
+ * [r·N/G, (r+1)·N/G)), spectrum in y-slabs of [N kx][N/G ky][N/2+1 kz] after the transpose.
+ * The NCCL exchanges between these calls are issued by nbody_b200/dist.py.
+ *
+ * nb_cic_deposit_slab / nb_gather_kick_drift_slab: K1 / K3 on a slab buffer
+ *   [nx_own + n_ghost][N][N] holding planes x0.. (mod N); ghost planes follow the own planes
+ *   (+x side; 1 plane, 2 with the half-cell interlace shift).  Particles outside the slab are
+ *   dropped and counted in n_outside (device int64, nullable) / gather zero.
+ * nb_kspace_fused_slab, nb_pk_bin_slab: K2 / K6 on the y-slab ky in [y0, y0+ny_local);
+ *   nb_pk_bin_slab ADDS into counts/sums (zero them first, all-reduce afterwards).
+ * nb_slab_fft2d: batched 2-D R2C (dir=+1) / C2R (dir=-1) over (y,z) of nplanes x-planes.
+ * nb_slab_fft1d_x: in-place 1-D C2C along x of spec[N][rows], dir = +1 forward / -1 inverse.
+ * nb_slab_pack:   [nxl][G][nyl·nzh] -> [G][nxl][nyl·nzh] (send layout of the forward transpose)
+ * nb_slab_unpack: [G][nxl][nyl·nzh] -> [nxl][G·nyl][nzh] (after the inverse transpose)
+ * nb_slab_owner: owner[p] = (int(x/cell) % N) / planes_per_rank with the deposit's float64
+ *   index math; counts (device int64[G], nullable) receives particles per owner.
+ * nb_grid_add: dst += src (float32; received ghost planes onto the first own planes). */
+int nb_cic_deposit_slab(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N, int x0,
+                        int nx_own, int n_ghost, float* grid, double shift, int accumulate,
+                        int64_t* n_outside, void* stream);
+int nb_gather_kick_drift_slab(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                              int x0, int nx_own, int n_ghost, double cell, double* pos, double* mom,
+                              double* acc_out, int64_t np, double gscale, double kick, double drift,
+                              double L, void* stream);
+int nb_kspace_fused_slab(nb_ctx* ctx, const void* rho1, const void* rho2, int N, int y0, int ny_local,
+                         const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                         double pref, void* g3, void* h3, void* stream);
+int nb_pk_bin_slab(nb_ctx* ctx, const void* spec, int N, int y0, int ny_local, const double* k2_tab,
+                   const double* sinc_tab, const double* thresh, double thresh_first,
+                   double thresh_last, double thresh_hi, int n_edges, int window_power, int clip_mode,
+                   double clip_val, double norm, int closed_last, int64_t* counts, double* sums,
+                   void* stream);
+int nb_slab_fft2d(nb_ctx* ctx, int N, int nplanes, int dir, void* real, void* spec, void* stream);
+int nb_slab_fft1d_x(nb_ctx* ctx, int N, int64_t rows, int dir, void* spec, void* stream);
+int nb_slab_pack(nb_ctx* ctx, const void* src, void* dst, int nxl, int G, int nyl, int nzh, void* stream);
+int nb_slab_unpack(nb_ctx* ctx, const void* src, void* dst, int nxl, int G, int nyl, int nzh, void* stream);
+int nb_slab_owner(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N, int planes_per_rank,
+                  int32_t* owner, int64_t* counts, int G, void* stream);
+int nb_grid_add(nb_ctx* ctx, float* dst, const float* src, int64_t n, void* stream);
 
 #ifdef __cplusplus
 }

@@ -45,8 +45,22 @@ PROTOTYPES = {
     "nb_pp_accel": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_i32, c_vp, c_vp]),
     "nb_cell_sort": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
-                             c_f64, c_f64, c_i32, c_vp, c_vp]),
-    "nb_p3m_count_pairs": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp]),
+                             c_f64, c_f64, c_i32, c_i64, c_vp, c_vp]),
+    "nb_p3m_count_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp]),
+    "nb_cic_deposit_slab": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_i32, c_i32, c_vp, c_f64, c_i32, c_vp,
+                                    c_vp]),
+    "nb_gather_kick_drift_slab": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_f64, c_vp, c_vp, c_vp,
+                                          c_i64, c_f64, c_f64, c_f64, c_f64, c_vp]),
+    "nb_kspace_fused_slab": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_f64, c_i32, c_f64, c_vp,
+                                     c_vp, c_vp]),
+    "nb_pk_bin_slab": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_f64, c_f64, c_f64, c_i32, c_i32,
+                               c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),
+    "nb_slab_fft2d": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "nb_slab_fft1d_x": (c_i32, [c_vp, c_i32, c_i64, c_i32, c_vp, c_vp]),
+    "nb_slab_pack": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp]),
+    "nb_slab_unpack": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp]),
+    "nb_slab_owner": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "nb_grid_add": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp]),
 }
 
 
@@ -72,13 +86,13 @@ def load():
         fn.restype = res
         fn.argtypes = args
     got = lib.nb_abi_version()
-    if got != 1 and got != ABI_VERSION:
+    if got != ABI_VERSION:
         raise ImportError(f"libnbody_b200.so ABI {got} != binding ABI {ABI_VERSION}")
     _lib = lib
     return lib
 
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 def check(rc: int, what: str = ""):

@@ -11,13 +11,23 @@ struct CicStencil {
   double w000, w001, w010, w011, w100, w101, w110, w111;
 };
 
-__device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, double cell, int N) {
+// x0 / nxp: first mesh plane and number of planes of the field buffer ([nxp][N][N]); the full
+// mesh has x0 = 0, nxp = N, a slab has nxp = own + ghost planes.  A stencil that does not fit
+// the buffer (a particle this slab does not own) gets zero weights on plane 0: no out-of-range
+// access, contributes nothing.
+__device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, double cell, int N, int x0 = 0,
+                                                  int nxp = 0x7fffffff) {
   CicStencil s;
   const int i0 = nb_cell_index(x, cell, N), j0 = nb_cell_index(y, cell, N);
   s.k0 = nb_cell_index(z, cell, N);
   const double dx = nb_cell_frac(x, cell), dy = nb_cell_frac(y, cell), dz = nb_cell_frac(z, cell);
-  const int i1 = nb_wrap1(i0, N), j1 = nb_wrap1(j0, N);
+  const int j1 = nb_wrap1(j0, N);
   s.k1 = nb_wrap1(s.k0, N);
+  int pa = i0 - x0, pb = nb_wrap1(i0, N) - x0;
+  pa = pa < 0 ? pa + N : pa;
+  pb = pb < 0 ? pb + N : pb;
+  const bool inside = pa < nxp && pb < nxp;
+  if (!inside) pa = pb = 0;
   const double wx0 = __dsub_rn(1.0, dx), wy0 = __dsub_rn(1.0, dy), wz0 = __dsub_rn(1.0, dz);
   const double w00 = __dmul_rn(wx0, wy0), w01 = __dmul_rn(wx0, dy);
   const double w10 = __dmul_rn(dx, wy0), w11 = __dmul_rn(dx, dy);
@@ -25,8 +35,9 @@ __device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, 
   s.w010 = __dmul_rn(w01, wz0); s.w011 = __dmul_rn(w01, dz);
   s.w100 = __dmul_rn(w10, wz0); s.w101 = __dmul_rn(w10, dz);
   s.w110 = __dmul_rn(w11, wz0); s.w111 = __dmul_rn(w11, dz);
-  s.r00 = ((int64_t)i0 * N + j0) * N; s.r01 = ((int64_t)i0 * N + j1) * N;
-  s.r10 = ((int64_t)i1 * N + j0) * N; s.r11 = ((int64_t)i1 * N + j1) * N;
+  s.r00 = ((int64_t)pa * N + j0) * N; s.r01 = ((int64_t)pa * N + j1) * N;
+  s.r10 = ((int64_t)pb * N + j0) * N; s.r11 = ((int64_t)pb * N + j1) * N;
+  if (!inside) s.w000 = s.w001 = s.w010 = s.w011 = s.w100 = s.w101 = s.w110 = s.w111 = 0.0;
   return s;
 }
 
@@ -84,20 +95,21 @@ kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const doub
 // Fused PM tail: gather the 3 force meshes (optionally a second, interlace-shifted set,
 // averaged), kick, drift, wrap.  One pass over the particle stream.
 __global__ void __launch_bounds__(256)
-gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, double cell,
-                         double shift2, double* __restrict__ pos, double* __restrict__ mom,
+gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, int x0, int nxp,
+                         double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
                          double* __restrict__ acc_out, int64_t np, double gscale, double kick, double drift,
                          double L) {
-  const int64_t n3 = (int64_t)N * N * N;
+  const int64_t n3 = (int64_t)(nxp < N ? nxp : N) * N * N;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
     const double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
-    const CicStencil s = cic_stencil(x, y, z, cell, N);
+    const CicStencil s = cic_stencil(x, y, z, cell, N, x0, nxp);
     double g[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) g[c] = cic_interp(f1 + c * n3, s);
     if (f2) {
-      const CicStencil s2 = cic_stencil(__dadd_rn(x, shift2), __dadd_rn(y, shift2), __dadd_rn(z, shift2), cell, N);
+      const CicStencil s2 =
+          cic_stencil(__dadd_rn(x, shift2), __dadd_rn(y, shift2), __dadd_rn(z, shift2), cell, N, x0, nxp);
 #pragma unroll
       for (int c = 0; c < 3; ++c) g[c] = 0.5 * (g[c] + cic_interp(f2 + c * n3, s2));
     }
@@ -160,17 +172,35 @@ extern "C" int nb_kick_drift(nb_ctx* ctx, double* pos, double* mom, const double
   return NB_OK;
 }
 
-extern "C" int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
-                                    double cell, double* pos, double* mom, double* acc_out, int64_t np,
-                                    double gscale, double kick, double drift, double L, void* stream) {
+static int gkd_launch(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N, int x0, int nxp,
+                      double cell, double* pos, double* mom, double* acc_out, int64_t np, double gscale,
+                      double kick, double drift, double L, cudaStream_t st) {
   NB_REQUIRE(ctx && force3 && (np == 0 || pos), "NULL argument");
   NB_REQUIRE(N >= 1 && cell > 0 && L > 0, "bad N / cell / L");
   NB_REQUIRE(mom || acc_out, "nothing to do: give mom (kick+drift) and/or acc_out");
   if (np == 0) return NB_OK;
-  cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   gather_kick_drift_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(
-      force3, force3_shifted, N, cell, 0.5 * cell, pos, mom, acc_out, np, gscale, kick, drift, L);
+      force3, force3_shifted, N, x0, nxp, cell, 0.5 * cell, pos, mom, acc_out, np, gscale, kick, drift, L);
   NB_LAUNCHED(ctx);
   return NB_OK;
+}
+
+extern "C" int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                                    double cell, double* pos, double* mom, double* acc_out, int64_t np,
+                                    double gscale, double kick, double drift, double L, void* stream) {
+  return gkd_launch(ctx, force3, force3_shifted, N, 0, N, cell, pos, mom, acc_out, np, gscale, kick, drift, L,
+                    (cudaStream_t)stream);
+}
+
+// Slab form: force3 / force3_shifted are [3][nx_own + n_ghost][N][N] and hold the mesh planes
+// x0 .. x0 + nx_own + n_ghost - 1 (mod N); the ghost planes are copies of the next slab's
+// first planes (1 needed, 2 with the half-cell interlace shift).
+extern "C" int nb_gather_kick_drift_slab(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                                         int x0, int nx_own, int n_ghost, double cell, double* pos, double* mom,
+                                         double* acc_out, int64_t np, double gscale, double kick, double drift,
+                                         double L, void* stream) {
+  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && n_ghost >= 0 && nx_own + n_ghost <= N, "bad slab");
+  return gkd_launch(ctx, force3, force3_shifted, N, x0, nx_own + n_ghost, cell, pos, mom, acc_out, np, gscale,
+                    kick, drift, L, (cudaStream_t)stream);
 }

@@ -14,7 +14,7 @@
 #define KS_WARPS 8
 
 __global__ void __launch_bounds__(KS_WARPS * 32)
-kspace_fused_kernel(const float2* __restrict__ rho1, const float2* __restrict__ rho2, int N,
+kspace_fused_kernel(const float2* __restrict__ rho1, const float2* __restrict__ rho2, int N, int y0, int nyl,
                     const double* __restrict__ kv, const double* __restrict__ sinc, double r_s,
                     int deconv_order, float pref, float2* __restrict__ gx, float2* __restrict__ gy,
                     float2* __restrict__ gz, float2* __restrict__ hx, float2* __restrict__ hy,
@@ -44,10 +44,12 @@ kspace_fused_kernel(const float2* __restrict__ rho1, const float2* __restrict__ 
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nzh = N / 2 + 1;
-  const int64_t nrows = (int64_t)N * N;
+  // spectra are [N (kx)][nyl (ky = y0 .. y0+nyl-1)][N/2+1 (kz)]: the whole half spectrum
+  // (y0 = 0, nyl = N) or the y-slab a rank holds after the slab-FFT transpose
+  const int64_t nrows = (int64_t)N * nyl;
   const int64_t wstride = (int64_t)gridDim.x * KS_WARPS;
   for (int64_t row = (int64_t)blockIdx.x * KS_WARPS + warp; row < nrows; row += wstride) {
-    const int j = (int)(row % N), i = (int)(row / N);
+    const int j = y0 + (int)(row % nyl), i = (int)(row / nyl);
     const float kgx = s_kg[i], kgy = s_kg[j];
     const float k2xy = s_k2[i] + s_k2[j];
     const float txy = s_t[i] * s_t[j] * pref;
@@ -88,27 +90,43 @@ kspace_fused_kernel(const float2* __restrict__ rho1, const float2* __restrict__ 
 
 // rho_k (half spectrum, cuFFT R2C layout) -> 3 (or 6) force spectra.  Exposed for the
 // slab-decomposed path and for tests; nb_pm_force_mesh is the single-GPU composition.
-extern "C" int nb_kspace_fused(nb_ctx* ctx, const void* rho1, const void* rho2, int N, const double* k_vals,
-                               const double* sinc_tab, double r_s, int deconv_order, double pref,
-                               void* g3, void* h3, void* stream) {
+static int kspace_launch(nb_ctx* ctx, const void* rho1, const void* rho2, int N, int y0, int nyl,
+                         const double* k_vals, const double* sinc_tab, double r_s, int deconv_order, double pref,
+                         void* g3, void* h3, cudaStream_t st) {
   NB_REQUIRE(ctx && rho1 && k_vals && sinc_tab && g3, "NULL argument");
   NB_REQUIRE(N >= 2 && N <= 8192, "bad N");
+  NB_REQUIRE(y0 >= 0 && nyl >= 1 && y0 + nyl <= N, "bad y-slab");
   NB_REQUIRE(deconv_order >= 0 && deconv_order <= 2, "deconv_order must be 0, 1 or 2");
-  cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
-  const int64_t nspec = (int64_t)N * N * (N / 2 + 1);
+  const int64_t nspec = (int64_t)N * nyl * (N / 2 + 1);
   const size_t smem = 5 * sizeof(float) * (size_t)N;
   NB_CHECK_CUDA(cudaFuncSetAttribute(kspace_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int nblk = ctx->num_sms * 4;
-  const int64_t need = ((int64_t)N * N + KS_WARPS - 1) / KS_WARPS;
+  const int64_t need = ((int64_t)N * nyl + KS_WARPS - 1) / KS_WARPS;
   if (nblk > need) nblk = (int)need;
   float2* g = (float2*)g3;
   float2* h = (float2*)h3;
   kspace_fused_kernel<<<nblk, KS_WARPS * 32, smem, st>>>(
-      (const float2*)rho1, (const float2*)rho2, N, k_vals, sinc_tab, r_s, deconv_order, (float)pref, g, g + nspec,
-      g + 2 * nspec, h, h ? h + nspec : nullptr, h ? h + 2 * nspec : nullptr);
+      (const float2*)rho1, (const float2*)rho2, N, y0, nyl, k_vals, sinc_tab, r_s, deconv_order, (float)pref, g,
+      g + nspec, g + 2 * nspec, h, h ? h + nspec : nullptr, h ? h + 2 * nspec : nullptr);
   NB_LAUNCHED(ctx);
   return NB_OK;
+}
+
+extern "C" int nb_kspace_fused(nb_ctx* ctx, const void* rho1, const void* rho2, int N, const double* k_vals,
+                               const double* sinc_tab, double r_s, int deconv_order, double pref,
+                               void* g3, void* h3, void* stream) {
+  return kspace_launch(ctx, rho1, rho2, N, 0, N, k_vals, sinc_tab, r_s, deconv_order, pref, g3, h3,
+                       (cudaStream_t)stream);
+}
+
+// Slab form: spectra are [N][ny_local][N/2+1] with ky = y0 + local index (transposed layout
+// of the slab FFT); g3 / h3 are 3 consecutive spectra of that shape.
+extern "C" int nb_kspace_fused_slab(nb_ctx* ctx, const void* rho1, const void* rho2, int N, int y0, int ny_local,
+                                    const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                                    double pref, void* g3, void* h3, void* stream) {
+  return kspace_launch(ctx, rho1, rho2, N, y0, ny_local, k_vals, sinc_tab, r_s, deconv_order, pref, g3, h3,
+                       (cudaStream_t)stream);
 }
 
 // Single-GPU long-range solve: deposit -> R2C -> [shifted deposit -> R2C] -> K2 -> 3 (6) C2R.

@@ -12,6 +12,8 @@
 // Split factor: 1 - u³·Q(u²) with Q a degree-10 polynomial in t = 2u²/u_max² - 1 (host-fitted
 // Chebyshev interpolant; |error| < 3e-7 absolute, the float32 floor).
 // FP32 in the pair loop, float64 accumulation across neighbour cells.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #define P3M_WARPS 4
@@ -35,7 +37,7 @@ __device__ __forceinline__ float p3m_rsqrt(float x) {
 __global__ void __launch_bounds__(P3M_WARPS * 32)
 p3m_short_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                  const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
-                 double scale, double* __restrict__ acc, int accumulate) {
+                 double scale, double* __restrict__ acc, int accumulate, int i_limit) {
   __shared__ float4 jbuf[P3M_WARPS][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t wstride = (int64_t)gridDim.x * P3M_WARPS;
@@ -47,8 +49,11 @@ p3m_short_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
     const int cx = (int)(c / ((int64_t)ncs * ncs));
     for (int ib = is; ib < ie; ib += 32) {
       const int i = ib + lane;
-      const bool ivalid = i < ie;
-      const float4 pi = sorted[ivalid ? i : is];
+      // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+      const int oi = i < ie ? perm[i] : 0x7fffffff;
+      const bool ivalid = oi < i_limit;
+      if (!__any_sync(0xffffffffu, ivalid)) continue;
+      const float4 pi = sorted[i < ie ? i : is];
       double ax = 0.0, ay = 0.0, az = 0.0;
       for (int ox = -1; ox <= 1; ++ox) {
         int nx = cx + ox;
@@ -99,7 +104,239 @@ p3m_short_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
         }
       }
       if (ivalid) {
-        const int64_t o = perm[i];
+        const int64_t o = oi;
+        if (accumulate) {
+          acc[3 * o] += ax * scale; acc[3 * o + 1] += ay * scale; acc[3 * o + 2] += az * scale;
+        } else {
+          acc[3 * o] = ax * scale; acc[3 * o + 1] = ay * scale; acc[3 * o + 2] = az * scale;
+        }
+      }
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------
+// v2 — "uniform i, lanes over j" with in-range compaction (experimental, NB_P3M_KERNEL=2).
+//
+// The v1 kernel above evaluates the full split polynomial for every candidate pair of the 27
+// neighbour cells although only ~16 % of them are inside r_cut (27 cs³ against 4.19 r_cut³):
+// measured 61 issue slots per candidate on B200.  v2 separates the cheap test from the
+// expensive evaluation:
+//   tile build  the j-particles of all 27 neighbour cells are copied once per (cell, i-block)
+//               into a per-warp SoA shared-memory tile, already translated into the frame of
+//               the i-cell (periodic wrap costs nothing later);
+//   phase 1     for one i-particle (warp-uniform, broadcast by shuffle) the 32 lanes test 64
+//               candidates per iteration with packed FP32 (LDS.64 + FADD2/FFMA2), and the
+//               in-range separations (dx,dy,dz) are compacted with ballot/popc into a
+//               per-warp list — conflict-free, no atomics;
+//   phase 2     the list is drained 32 pairs at a time with every lane busy: softened
+//               rsqrt, split polynomial (two interleaved Horner chains), FMA accumulation;
+//   reduce      one xor-shuffle reduction per i-particle, added to the float64 accumulator
+//               held by the lane that owns that i-particle.
+// sorted_xyzw.w (the mass) must be uniform: nb_cell_sort writes the scalar `mass` there.
+#define P3M2_WARPS 4
+#define P3M2_CAP 896     // candidate tile capacity per warp (multiple of 64)
+#define P3M2_LCAP 256    // in-range list capacity per warp
+#define P3M2_FLOATS_PER_WARP (3 * P3M2_CAP + 3 * P3M2_LCAP)
+
+typedef unsigned long long p3m_f32x2;
+__device__ __forceinline__ p3m_f32x2 p3m_pack2(float lo, float hi) {
+  p3m_f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void p3m_unpack2(p3m_f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ p3m_f32x2 p3m_add2(p3m_f32x2 a, p3m_f32x2 b) {
+  p3m_f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ p3m_f32x2 p3m_mul2(p3m_f32x2 a, p3m_f32x2 b) {
+  p3m_f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ p3m_f32x2 p3m_fma2(p3m_f32x2 a, p3m_f32x2 b, p3m_f32x2 c) {
+  p3m_f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
+// phase 2: evaluate the `cnt` compacted separations, 32 per iteration
+__device__ __forceinline__ void p3m2_drain(const float* __restrict__ lx, const float* __restrict__ ly,
+                                           const float* __restrict__ lz, int cnt, int lane, const P3mParams& prm,
+                                           float wj, float& fx, float& fy, float& fz) {
+  __syncwarp();
+  for (int q0 = 0; q0 < cnt; q0 += 32) {
+    const int q = q0 + lane;
+    if (q < cnt) {
+      const float dx = lx[q], dy = ly[q], dz = lz[q];
+      float r2 = dx * dx;
+      r2 = fmaf(dy, dy, r2);
+      r2 = fmaf(dz, dz, r2);
+      // coincident points (the self pair): d = 0, the clamp keeps rinv³ finite -> contributes 0
+      const float rinv = p3m_rsqrt(fmaxf(r2 + prm.eps2, 1e-20f));
+      const float w = r2 * prm.w_scale;                 // u²
+      const float u = w * p3m_rsqrt(fmaxf(w, 1e-30f));
+      const float tt = fmaf(w, prm.t_scale, -1.f);
+      const float t2 = tt * tt;
+      float qe = prm.coef[10], qo = prm.coef[9];
+      qe = fmaf(qe, t2, prm.coef[8]); qo = fmaf(qo, t2, prm.coef[7]);
+      qe = fmaf(qe, t2, prm.coef[6]); qo = fmaf(qo, t2, prm.coef[5]);
+      qe = fmaf(qe, t2, prm.coef[4]); qo = fmaf(qo, t2, prm.coef[3]);
+      qe = fmaf(qe, t2, prm.coef[2]); qo = fmaf(qo, t2, prm.coef[1]);
+      qe = fmaf(qe, t2, prm.coef[0]);
+      const float qq = fmaf(qo, tt, qe);
+      const float f = fmaf(-(w * u), qq, 1.f);          // erfc(u) + 2u/sqrt(pi) exp(-u²)
+      const float s = (wj * rinv) * (rinv * rinv) * f;
+      fx = fmaf(s, dx, fx);
+      fy = fmaf(s, dy, fy);
+      fz = fmaf(s, dz, fz);
+    }
+  }
+  __syncwarp();
+}
+
+// all i-particles of the block against the `nt` candidates in the tile
+__device__ __forceinline__ void p3m2_process(float* __restrict__ tx, float* __restrict__ ty, float* __restrict__ tz,
+                                             float* __restrict__ lx, float* __restrict__ ly, float* __restrict__ lz,
+                                             int nt, int nib, const float4& pi, int lane, const P3mParams& prm,
+                                             float wj, double& ax, double& ay, double& az) {
+  const int ntpad = (nt + 63) & ~63;
+  for (int t = nt + lane; t < ntpad; t += 32) {   // sentinels: far outside any cutoff
+    tx[t] = 1e18f;
+    ty[t] = 0.f;
+    tz[t] = 0.f;
+  }
+  __syncwarp();
+  const unsigned lt = (1u << lane) - 1u;
+  for (int ii = 0; ii < nib; ++ii) {
+    const float xi = __shfl_sync(0xffffffffu, pi.x, ii);
+    const float yi = __shfl_sync(0xffffffffu, pi.y, ii);
+    const float zi = __shfl_sync(0xffffffffu, pi.z, ii);
+    const p3m_f32x2 nx2 = p3m_pack2(-xi, -xi), ny2 = p3m_pack2(-yi, -yi), nz2 = p3m_pack2(-zi, -zi);
+    int cnt = 0;
+    float fx = 0.f, fy = 0.f, fz = 0.f;
+#pragma unroll 2
+    for (int v = 0; v < ntpad; v += 64) {
+      const p3m_f32x2 X = *reinterpret_cast<const p3m_f32x2*>(tx + v + 2 * lane);
+      const p3m_f32x2 Y = *reinterpret_cast<const p3m_f32x2*>(ty + v + 2 * lane);
+      const p3m_f32x2 Z = *reinterpret_cast<const p3m_f32x2*>(tz + v + 2 * lane);
+      const p3m_f32x2 dx = p3m_add2(X, nx2), dy = p3m_add2(Y, ny2), dz = p3m_add2(Z, nz2);
+      p3m_f32x2 r2 = p3m_mul2(dx, dx);
+      r2 = p3m_fma2(dy, dy, r2);
+      r2 = p3m_fma2(dz, dz, r2);
+      float r2a, r2b;
+      p3m_unpack2(r2, r2a, r2b);
+      const bool in0 = r2a < prm.rc2, in1 = r2b < prm.rc2;
+      const unsigned m0 = __ballot_sync(0xffffffffu, in0);
+      const unsigned m1 = __ballot_sync(0xffffffffu, in1);
+      const int c0 = __popc(m0);
+      if (in0) {
+        const int p = cnt + __popc(m0 & lt);
+        float a, b;
+        p3m_unpack2(dx, a, b); lx[p] = a;
+        p3m_unpack2(dy, a, b); ly[p] = a;
+        p3m_unpack2(dz, a, b); lz[p] = a;
+      }
+      if (in1) {
+        const int p = cnt + c0 + __popc(m1 & lt);
+        float a, b;
+        p3m_unpack2(dx, a, b); lx[p] = b;
+        p3m_unpack2(dy, a, b); ly[p] = b;
+        p3m_unpack2(dz, a, b); lz[p] = b;
+      }
+      cnt += c0 + __popc(m1);
+      if (cnt > P3M2_LCAP - 64) {
+        p3m2_drain(lx, ly, lz, cnt, lane, prm, wj, fx, fy, fz);
+        cnt = 0;
+      }
+    }
+    p3m2_drain(lx, ly, lz, cnt, lane, prm, wj, fx, fy, fz);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      fx += __shfl_xor_sync(0xffffffffu, fx, o);
+      fy += __shfl_xor_sync(0xffffffffu, fy, o);
+      fz += __shfl_xor_sync(0xffffffffu, fz, o);
+    }
+    if (lane == ii) {
+      ax += (double)fx;
+      ay += (double)fy;
+      az += (double)fz;
+    }
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(P3M2_WARPS * 32)
+p3m_short_v2_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                    const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit) {
+  extern __shared__ __align__(16) float p3m2_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* tx = p3m2_smem + warp * P3M2_FLOATS_PER_WARP;
+  float* ty = tx + P3M2_CAP;
+  float* tz = ty + P3M2_CAP;
+  float* lx = tz + P3M2_CAP;
+  float* ly = lx + P3M2_LCAP;
+  float* lz = ly + P3M2_LCAP;
+  const float wj = __ldg(&sorted[0].w);   // uniform mass (nb_cell_sort)
+  const int64_t wstride = (int64_t)gridDim.x * P3M2_WARPS;
+  for (int64_t c = cell_lo + (int64_t)blockIdx.x * P3M2_WARPS + warp; c < cell_hi; c += wstride) {
+    const int is = cell_start[c], ie = cell_start[c + 1];
+    if (is == ie) continue;
+    const int cz = (int)(c % ncs);
+    const int cy = (int)((c / ncs) % ncs);
+    const int cx = (int)(c / ((int64_t)ncs * ncs));
+    // lanes 0..26 look up the j-ranges of the 27 neighbour cells
+    int my_js = 0, my_je = 0;
+    if (lane < 27) {
+      int nx = cx + lane / 9 - 1, ny = cy + (lane / 3) % 3 - 1, nz = cz + lane % 3 - 1;
+      nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+      ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+      nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+      const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+      my_js = cell_start[n];
+      my_je = cell_start[n + 1];
+    }
+    for (int ib = is; ib < ie; ib += 32) {
+      const int i = ib + lane;
+      // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+      const int oi = i < ie ? perm[i] : 0x7fffffff;
+      const bool ivalid = oi < i_limit;
+      if (!__any_sync(0xffffffffu, ivalid)) continue;
+      const float4 pi = sorted[i < ie ? i : is];
+      const int nib = min(32, ie - ib);
+      double ax = 0.0, ay = 0.0, az = 0.0;
+      int fill = 0;
+      for (int n = 0; n < 27; ++n) {
+        int js = __shfl_sync(0xffffffffu, my_js, n);
+        const int je = __shfl_sync(0xffffffffu, my_je, n);
+        const float offx = (float)(n / 9 - 1) * prm.cs;
+        const float offy = (float)((n / 3) % 3 - 1) * prm.cs;
+        const float offz = (float)(n % 3 - 1) * prm.cs;
+        while (js < je) {
+          const int take = min(je - js, P3M2_CAP - fill);
+          for (int t = lane; t < take; t += 32) {
+            const float4 p = sorted[js + t];
+            tx[fill + t] = p.x + offx;
+            ty[fill + t] = p.y + offy;
+            tz[fill + t] = p.z + offz;
+          }
+          fill += take;
+          js += take;
+          if (fill == P3M2_CAP) {
+            p3m2_process(tx, ty, tz, lx, ly, lz, fill, nib, pi, lane, prm, wj, ax, ay, az);
+            fill = 0;
+          }
+        }
+      }
+      if (fill > 0) p3m2_process(tx, ty, tz, lx, ly, lz, fill, nib, pi, lane, prm, wj, ax, ay, az);
+      if (ivalid) {
+        const int64_t o = oi;
         if (accumulate) {
           acc[3 * o] += ax * scale; acc[3 * o + 1] += ay * scale; acc[3 * o + 2] += az * scale;
         } else {
@@ -114,7 +351,7 @@ p3m_short_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
 extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
                             int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
                             double r_s, double eps, const double* coef_host, int ncoef, double u_max,
-                            double scale, int accumulate, double* acc, void* stream) {
+                            double scale, int accumulate, int64_t i_limit, double* acc, void* stream) {
   NB_REQUIRE(ctx && sorted_xyzw && cell_start && perm && coef_host && acc, "NULL argument");
   NB_REQUIRE(ncoef == P3M_DEG + 1, "split polynomial must have 11 coefficients");
   NB_REQUIRE(ncs >= 3, "need at least 3 cells per side (27 distinct neighbours)");
@@ -132,12 +369,25 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   prm.t_scale = (float)(2.0 / (u_max * u_max));
   prm.cs = (float)cell_side;
   for (int d = 0; d <= P3M_DEG; ++d) prm.coef[d] = (float)coef_host[d];
+  const int ilim = (i_limit <= 0 || i_limit > 0x7fffffff) ? 0x7fffffff : (int)i_limit;
   const int64_t ncell = cell_hi - cell_lo;
-  int64_t nblk = (ncell + P3M_WARPS - 1) / P3M_WARPS;
   const int64_t cap = (int64_t)ctx->num_sms * 64;
-  if (nblk > cap) nblk = cap;
-  p3m_short_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo,
-                                                         cell_hi, prm, scale, acc, accumulate);
+  // v1 (warp-per-cell, lanes over i) is the default: 138.6 ms at BASELINE config 5 against
+  // 160.6 ms for v2 (profiles/r1b_*).  NB_P3M_KERNEL=2 selects v2 for A/B measurements.
+  static const int use_v1 = [] { const char* e = getenv("NB_P3M_KERNEL"); return !(e && atoi(e) == 2); }();
+  if (use_v1) {
+    int64_t nblk = (ncell + P3M_WARPS - 1) / P3M_WARPS;
+    if (nblk > cap) nblk = cap;
+    p3m_short_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo,
+                                                           cell_hi, prm, scale, acc, accumulate, ilim);
+  } else {
+    const size_t smem = sizeof(float) * P3M2_WARPS * P3M2_FLOATS_PER_WARP;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t nblk = (ncell + P3M2_WARPS - 1) / P3M2_WARPS;
+    if (nblk > cap) nblk = cap;
+    p3m_short_v2_kernel<<<(int)nblk, P3M2_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
+                                                                  cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
+  }
   NB_LAUNCHED(ctx);
   return NB_OK;
 }
@@ -146,8 +396,9 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
 // time into candidate-pair and in-range-pair rates): out[0] = candidate pairs, out[1] = pairs
 // with 0 < r < r_cut.
 __global__ void __launch_bounds__(P3M_WARPS * 32)
-p3m_count_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start, int ncs, int64_t cell_lo,
-                 int64_t cell_hi, float cs, float rc2, unsigned long long* __restrict__ out) {
+p3m_count_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                 const int* __restrict__ perm, int i_limit, int ncs, int64_t cell_lo, int64_t cell_hi, float cs,
+                 float rc2, unsigned long long* __restrict__ out) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t wstride = (int64_t)gridDim.x * P3M_WARPS;
   unsigned long long cand = 0, inr = 0;
@@ -156,6 +407,7 @@ p3m_count_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
     if (is == ie) continue;
     const int cz = (int)(c % ncs), cy = (int)((c / ncs) % ncs), cx = (int)(c / ((int64_t)ncs * ncs));
     for (int i = is + lane; i < ie; i += 32) {
+      if (perm && perm[i] >= i_limit) continue;   // halo copy: a source, not an i-particle
       const float4 pi = sorted[i];
       for (int ox = -1; ox <= 1; ++ox)
         for (int oy = -1; oy <= 1; ++oy)
@@ -183,9 +435,9 @@ p3m_count_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell
   }
 }
 
-extern "C" int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, int ncs,
-                                  int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
-                                  int64_t* out2, void* stream) {
+extern "C" int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start,
+                                  const int32_t* perm, int64_t i_limit, int ncs, int64_t cell_lo, int64_t cell_hi,
+                                  double cell_side, double r_cut, int64_t* out2, void* stream) {
   NB_REQUIRE(ctx && sorted_xyzw && cell_start && out2, "NULL argument");
   NB_REQUIRE(ncs >= 3 && cell_lo >= 0 && cell_lo <= cell_hi && cell_hi <= (int64_t)ncs * ncs * ncs, "bad cells");
   cudaStream_t st = (cudaStream_t)stream;
@@ -195,7 +447,9 @@ extern "C" int nb_p3m_count_pairs(nb_ctx* ctx, const void* sorted_xyzw, const in
   int64_t nblk = (cell_hi - cell_lo + P3M_WARPS - 1) / P3M_WARPS;
   const int64_t cap = (int64_t)ctx->num_sms * 64;
   if (nblk > cap) nblk = cap;
-  p3m_count_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start, ncs, cell_lo, cell_hi,
+  const int ilim = (i_limit <= 0 || i_limit > 0x7fffffff) ? 0x7fffffff : (int)i_limit;
+  p3m_count_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start,
+                                                         i_limit > 0 ? perm : nullptr, ilim, ncs, cell_lo, cell_hi,
                                                          (float)cell_side, (float)(r_cut * r_cut),
                                                          (unsigned long long*)out2);
   NB_LAUNCHED(ctx);

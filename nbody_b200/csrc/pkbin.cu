@@ -21,7 +21,7 @@
 
 template <typename C, typename T>
 __global__ void __launch_bounds__(PK_WARPS * 32)
-pk_shell_bin_kernel(const C* __restrict__ spec, int N, const double* __restrict__ k2_tab,
+pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const double* __restrict__ k2_tab,
                     const double* __restrict__ sinc_tab, const double* __restrict__ thresh,
                     double thresh_hi, int n_edges, int window_power, int clip_mode, double clip_val,
                     double norm, int closed_last, float log2_k2min, float inv_dlog2,
@@ -50,11 +50,11 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, const double* __restrict_
   const int kz_nyq = (N % 2 == 0) ? N / 2 : -1;
   double* my_sums = s_sums + warp * nb;
   unsigned* my_cnt = s_cnt + warp * nb;
-  const int64_t nrows = (int64_t)N * N;
+  const int64_t nrows = (int64_t)N * nyl;   // spec is [N (kx)][nyl (ky = y0..)][N/2+1]
   const int64_t wstride = (int64_t)gridDim.x * PK_WARPS;
 
   for (int64_t row = (int64_t)blockIdx.x * PK_WARPS + warp; row < nrows; row += wstride) {
-    const int j = (int)(row % N), i = (int)(row / N);
+    const int j = y0 + (int)(row % nyl), i = (int)(row / nyl);
     const double kxy2 = __dadd_rn(s_k2[i], s_k2[j]);
     const double sxy = __dmul_rn(s_sinc[i], s_sinc[j]);
     const C* rowp = spec + row * nzh;
@@ -135,7 +135,7 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, const double* __restrict_
 
 // Bins the half spectrum `spec` ([N][N][N/2+1]) — shared by nb_power_spectrum and the
 // slab-decomposed path.
-int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int prec, const double* k2_tab,
+int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, int prec, const double* k2_tab,
                        const double* sinc_tab, const double* thresh, double thresh_hi, int n_edges,
                        int window_power, int clip_mode, double clip_val, double norm, int closed_last,
                        double k2min_host, double k2max_host, int64_t* counts, double* sums,
@@ -148,18 +148,18 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int prec, const dou
   const float log2_k2min = (float)log2(k2min_host);
   const float inv_dlog2 = (float)((double)(n_edges - 1) / (log2(k2max_host) - log2(k2min_host)));
   int nblk = ctx->num_sms * 2;
-  const int64_t need = ((int64_t)N * N + PK_WARPS - 1) / PK_WARPS;
+  const int64_t need = ((int64_t)N * nyl + PK_WARPS - 1) / PK_WARPS;
   if (nblk > need) nblk = (int)need;
   if (prec == NB_F64) {
     auto kern = pk_shell_bin_kernel<double2, double>;
     NB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<nblk, PK_WARPS * 32, smem, st>>>((const double2*)spec, N, k2_tab, sinc_tab, thresh, thresh_hi,
+    kern<<<nblk, PK_WARPS * 32, smem, st>>>((const double2*)spec, N, y0, nyl, k2_tab, sinc_tab, thresh, thresh_hi,
                                             n_edges, window_power, clip_mode, clip_val, norm, closed_last,
                                             log2_k2min, inv_dlog2, (unsigned long long*)counts, sums);
   } else {
     auto kern = pk_shell_bin_kernel<float2, float>;
     NB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<nblk, PK_WARPS * 32, smem, st>>>((const float2*)spec, N, k2_tab, sinc_tab, thresh, thresh_hi,
+    kern<<<nblk, PK_WARPS * 32, smem, st>>>((const float2*)spec, N, y0, nyl, k2_tab, sinc_tab, thresh, thresh_hi,
                                             n_edges, window_power, clip_mode, clip_val, norm, closed_last,
                                             log2_k2min, inv_dlog2, (unsigned long long*)counts, sums);
   }
@@ -197,6 +197,23 @@ extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec
   NB_CHECK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * (n_edges - 1), st));
   NB_REQUIRE(thresh_first > 0 && thresh_last > thresh_first, "bin thresholds must be positive and increasing");
   NbPhase ph(ctx, NB_PH_PK_BIN, st);
-  return nb_pk_bin_spectrum(ctx, spec, N, prec, k2_tab, sinc_tab, thresh, thresh_hi, n_edges, window_power,
+  return nb_pk_bin_spectrum(ctx, spec, N, 0, N, prec, k2_tab, sinc_tab, thresh, thresh_hi, n_edges, window_power,
                             clip_mode, clip_val, norm, closed_last, thresh_first, thresh_last, counts, sums, st);
+}
+
+// Slab form: bins the y-slab [N][ny_local][N/2+1] (complex64) a rank holds after the slab-FFT
+// transpose and ADDS into counts / sums (the caller zeroes them and all-reduces afterwards).
+extern "C" int nb_pk_bin_slab(nb_ctx* ctx, const void* spec, int N, int y0, int ny_local, const double* k2_tab,
+                              const double* sinc_tab, const double* thresh, double thresh_first,
+                              double thresh_last, double thresh_hi, int n_edges, int window_power, int clip_mode,
+                              double clip_val, double norm, int closed_last, int64_t* counts, double* sums,
+                              void* stream) {
+  NB_REQUIRE(ctx && spec && k2_tab && sinc_tab && thresh && counts && sums, "NULL argument");
+  NB_REQUIRE(N >= 2 && n_edges >= 2 && y0 >= 0 && ny_local >= 1 && y0 + ny_local <= N, "bad N / n_edges / slab");
+  NB_REQUIRE(window_power >= 0 && window_power <= 2 && clip_mode >= 0 && clip_mode <= 2, "bad window options");
+  NB_REQUIRE(thresh_first > 0 && thresh_last > thresh_first, "bin thresholds must be positive and increasing");
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  return nb_pk_bin_spectrum(ctx, spec, N, y0, ny_local, NB_F32, k2_tab, sinc_tab, thresh, thresh_hi, n_edges,
+                            window_power, clip_mode, clip_val, norm, closed_last, thresh_first, thresh_last,
+                            counts, sums, (cudaStream_t)stream);
 }

@@ -304,7 +304,7 @@ class Engine:
 
     def p3m_short(self, sorted4, perm, cell_start, L: float, ncs: int, r_s: float, r_cut: float, eps: float,
                   scale: float, out: torch.Tensor, accumulate: bool = False, cell_lo: int = 0,
-                  cell_hi: int | None = None) -> torch.Tensor:
+                  cell_hi: int | None = None, i_limit: int = 0) -> torch.Tensor:
         u_max = r_cut / (2 * r_s) * 1.0001
         key = ("split", round(u_max, 9))
         if key not in self._tab_cache:
@@ -315,17 +315,98 @@ class Engine:
         _lib.check(self.lib.nb_p3m_short(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm), int(ncs),
                                          int(cell_lo), int(cell_hi), L / ncs, float(r_cut), float(r_s), float(eps),
                                          coef.ctypes.data_as(C.c_void_p), int(coef.size), float(u_max),
-                                         float(scale), int(bool(accumulate)), _ptr(out), self.stream),
+                                         float(scale), int(bool(accumulate)), int(i_limit), _ptr(out), self.stream),
                    "nb_p3m_short")
         return out
 
-    def p3m_count_pairs(self, sorted4, cell_start, L: float, ncs: int, r_cut: float, cell_lo=0, cell_hi=None):
+    def p3m_count_pairs(self, sorted4, cell_start, L: float, ncs: int, r_cut: float, cell_lo=0, cell_hi=None,
+                        perm=None, i_limit: int = 0):
         out = torch.empty(2, dtype=torch.int64, device=self.device)
-        _lib.check(self.lib.nb_p3m_count_pairs(self.ctx, _ptr(sorted4), _ptr(cell_start), int(ncs), int(cell_lo),
+        _lib.check(self.lib.nb_p3m_count_pairs(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm),
+                                               int(i_limit if perm is not None else 0), int(ncs), int(cell_lo),
                                                int(ncs ** 3 if cell_hi is None else cell_hi), L / ncs,
                                                float(r_cut), _ptr(out), self.stream), "nb_p3m_count_pairs")
         c = out.cpu().numpy()
         return int(c[0]), int(c[1])
+
+    # -- slab decomposition (dist.py) ----------------------------------------------------------
+    def cic_deposit_slab(self, pos, cell, N, x0, nx_own, n_ghost, out, shift=0.0, accumulate=False,
+                         n_outside: torch.Tensor | None = None):
+        self._check_pos(pos)
+        if out.dtype != torch.float32 or out.numel() != (nx_own + n_ghost) * N * N or not out.is_contiguous():
+            raise ValueError("slab grid must be contiguous float32 [nx_own+n_ghost][N][N]")
+        _lib.check(self.lib.nb_cic_deposit_slab(self.ctx, _ptr(pos), pos.shape[0], float(cell), int(N), int(x0),
+                                                int(nx_own), int(n_ghost), _ptr(out), float(shift),
+                                                int(bool(accumulate)), _ptr(n_outside), self.stream),
+                   "nb_cic_deposit_slab")
+        return out
+
+    def gather_kick_drift_slab(self, force3, force3_shifted, N, x0, nx_own, n_ghost, cell, pos, mom, acc_out,
+                               gscale, kick, drift, L):
+        self._check_pos(pos)
+        _lib.check(self.lib.nb_gather_kick_drift_slab(self.ctx, _ptr(force3), _ptr(force3_shifted), int(N), int(x0),
+                                                      int(nx_own), int(n_ghost), float(cell), _ptr(pos), _ptr(mom),
+                                                      _ptr(acc_out), pos.shape[0], float(gscale), float(kick),
+                                                      float(drift), float(L), self.stream),
+                   "nb_gather_kick_drift_slab")
+
+    def kspace_fused_slab(self, rho1, rho2, L, N, y0, nyl, r_s, deconv_order, pref, g3, h3=None):
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        s = self.sinc_tab(N, L)
+        _lib.check(self.lib.nb_kspace_fused_slab(self.ctx, _ptr(rho1), _ptr(rho2), int(N), int(y0), int(nyl), _ptr(kv),
+                                                 _ptr(s), float(r_s), int(deconv_order), float(pref), _ptr(g3),
+                                                 _ptr(h3), self.stream), "nb_kspace_fused_slab")
+        return g3, h3
+
+    def pk_tables(self, N, L, n_edges, kq_form="inv_d"):
+        key = ("edges", N, float(L), n_edges)
+        if key not in self._tab_cache:
+            e = tables.pk_edges(N, L, n_edges)
+            thr, thr_hi = tables.sqrt_thresholds(e)
+            self._tab_cache[key] = (e, torch.from_numpy(thr).to(self.device), float(thr[0]), float(thr[-1]), thr_hi)
+        k2 = self.table(("k2", N, float(L)), lambda: tables.k_vals(N, L) ** 2)
+        return self._tab_cache[key] + (k2, self.sinc_tab(N, L, kq_form))
+
+    def pk_bin_slab(self, spec, L, N, y0, nyl, counts, sums, n_edges=300, window_power=0, clip_mode=0,
+                    clip_val=0.0, norm=1.0, closed_last=True, kq_form="inv_d"):
+        """Adds the shell sums of the y-slab spectrum [N][nyl][N/2+1] (complex64) into counts/sums."""
+        edges, thr_d, t0, t1, thr_hi, k2, s = self.pk_tables(N, L, n_edges, kq_form)
+        _lib.check(self.lib.nb_pk_bin_slab(self.ctx, _ptr(spec), int(N), int(y0), int(nyl), _ptr(k2), _ptr(s),
+                                           _ptr(thr_d), t0, t1, thr_hi, int(n_edges), int(window_power),
+                                           int(clip_mode), float(clip_val), float(norm), int(bool(closed_last)),
+                                           _ptr(counts), _ptr(sums), self.stream), "nb_pk_bin_slab")
+        return edges
+
+    def slab_fft2d(self, N, nplanes, direction, real, spec):
+        _lib.check(self.lib.nb_slab_fft2d(self.ctx, int(N), int(nplanes), int(direction), _ptr(real), _ptr(spec),
+                                          self.stream), "nb_slab_fft2d")
+
+    def slab_fft1d_x(self, N, rows, direction, spec):
+        _lib.check(self.lib.nb_slab_fft1d_x(self.ctx, int(N), int(rows), int(direction), _ptr(spec), self.stream),
+                   "nb_slab_fft1d_x")
+
+    def slab_pack(self, src, dst, nxl, G, nyl, nzh):
+        _lib.check(self.lib.nb_slab_pack(self.ctx, _ptr(src), _ptr(dst), int(nxl), int(G), int(nyl), int(nzh),
+                                         self.stream), "nb_slab_pack")
+
+    def slab_unpack(self, src, dst, nxl, G, nyl, nzh):
+        _lib.check(self.lib.nb_slab_unpack(self.ctx, _ptr(src), _ptr(dst), int(nxl), int(G), int(nyl), int(nzh),
+                                           self.stream), "nb_slab_unpack")
+
+    def slab_owner(self, pos, cell, N, planes_per_rank, G):
+        self._check_pos(pos)
+        owner = torch.empty(pos.shape[0], dtype=torch.int32, device=self.device)
+        counts = torch.empty(G, dtype=torch.int64, device=self.device)
+        _lib.check(self.lib.nb_slab_owner(self.ctx, _ptr(pos), pos.shape[0], float(cell), int(N),
+                                          int(planes_per_rank), _ptr(owner), _ptr(counts), int(G), self.stream),
+                   "nb_slab_owner")
+        return owner, counts
+
+    def grid_add(self, dst, src):
+        if dst.dtype != torch.float32 or src.dtype != torch.float32 or dst.numel() != src.numel():
+            raise ValueError("grid_add needs float32 tensors of equal size")
+        _lib.check(self.lib.nb_grid_add(self.ctx, _ptr(dst), _ptr(src), dst.numel(), self.stream), "nb_grid_add")
+        return dst
 
 
 _default: dict[int, Engine] = {}

@@ -1,0 +1,149 @@
+"""GPU parity of the slab-decomposed (multi-GPU) path, with the ranks emulated as threads on
+ONE device (nbody_b200.dist.ThreadComm): the sharded PM / P3M / PP accelerations, the kick-drift
+step with particle migration, and the slab P(k) must equal the single-GPU path and the float64
+oracle on the same inputs.  The real NCCL run (bench.py --gpus N) executes the same per-rank
+code with TorchComm in place of ThreadComm."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import zeldovich_particles
+from oracle import force as oforce
+from oracle import restate
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def cfg_for(method, n, N, L, **kw):
+    from nbody_b200.params import ForceConfig
+    return ForceConfig(method=method, npart=n ** 3, boxsize=L, gridsize=N, **kw)
+
+
+def err(a, ref):
+    return np.abs(a - ref).max() / np.sqrt((ref ** 2).mean())
+
+
+def owner_np(pos, L, N, world):
+    return ((pos[:, 0] / (L / N)).astype(np.int64) % N) // (N // world)
+
+
+def run_ranks(world, cfg, pos, fn, method=None):
+    """fn(stepper, pos_dev_shard, idx) on every emulated rank; returns list of results."""
+    from nbody_b200.dist import DistForceStepper, run_threaded
+    from nbody_b200.engine import Engine
+    method = method or cfg.method
+    if method == "pp":
+        chunk = (pos.shape[0] + world - 1) // world
+        idx = [np.arange(r * chunk, min(pos.shape[0], (r + 1) * chunk)) for r in range(world)]
+    else:
+        own = owner_np(pos, cfg.boxsize, cfg.gridsize, world)
+        idx = [np.nonzero(own == r)[0] for r in range(world)]
+
+    def body(comm):
+        torch.cuda.set_device(0)
+        eng = Engine(0)
+        st = DistForceStepper(cfg, eng, comm=comm)
+        p = eng.to_device(pos[idx[comm.rank]])
+        out = fn(st, p, idx[comm.rank])
+        torch.cuda.synchronize()
+        return out
+
+    return run_threaded(world, body), idx
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("method,interlace", [("pm", (False, False)), ("pm", (True, True)), ("p3m", (True, True))])
+def test_sharded_accel_matches_oracle(world, method, interlace):
+    L, n, N = 1000.0, 16, 32
+    pos = zeldovich_particles(n, L, seed=11)
+    cfg = cfg_for(method, n, N, L, interlace=interlace, deconvolve=(True, True), G=1.0, mass=2.0)
+    if method == "p3m" and world == 4:
+        cfg = cfg_for(method, n, 64, L, interlace=interlace, deconvolve=(True, True), G=1.0, mass=2.0)  # slab >= 2 r_cut
+    res, idx = run_ranks(world, cfg, pos, lambda st, p, i: st.accel(p).cpu().numpy())
+    a = np.empty_like(pos)
+    for r in range(world):
+        a[idx[r]] = res[r]
+    assert err(a, oforce.accel(cfg, pos)) <= TOL
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_pp(world):
+    L, n = 500.0, 10
+    pos = zeldovich_particles(n, L, seed=5)[:997]          # ragged: 997 is not divisible by the world size
+    cfg = cfg_for("pp", n, 0, L, G=1.5, mass=2.0)
+    cfg.npart = pos.shape[0]
+    res, idx = run_ranks(world, cfg, pos, lambda st, p, i: st.accel(p, n_total=pos.shape[0]).cpu().numpy())
+    a = np.vstack(res)
+    assert err(a, oforce.accel(cfg, pos)) <= TOL
+
+
+@pytest.mark.parametrize("method", ["pm", "p3m"])
+def test_sharded_step_with_migration(method):
+    """A large drift moves particles across slab faces: after the step every rank holds exactly
+    the particles of its slab and the union equals the oracle's step."""
+    world, L, n, N = 2, 500.0, 12, 24
+    pos = zeldovich_particles(n, L, seed=21)
+    rs = np.random.RandomState(1)
+    mom = rs.normal(scale=30.0, size=pos.shape)
+    cfg = cfg_for(method, n, N, L, interlace=(True, True), G=1.0, mass=1.5, a=0.5)
+
+    def fn(st, p, i):
+        m = st.eng.to_device(mom[i])
+        p2, m2 = st.step(p, m, 0.3, 0.7)
+        return p2.cpu().numpy(), m2.cpu().numpy()
+
+    res, idx = run_ranks(world, cfg, pos, fn)
+    acc = oforce.accel(cfg, pos)
+    pr, mr = oforce.kick_drift(pos, mom, acc, L, mass=cfg.mass, a=cfg.a, dt_kick=0.3, dt_drift=0.7)
+    got_p = np.vstack([r[0] for r in res])
+    got_m = np.vstack([r[1] for r in res])
+    assert got_p.shape == pr.shape
+    moved = sum(int((owner_np(pos[idx[r]], L, N, world) != owner_np(pr[idx[r]], L, N, world)).sum())
+                for r in range(world))
+    assert moved > 0, "test must exercise migration"
+    for r in range(world):     # ownership after migration
+        assert (owner_np(res[r][0], L, N, world) == r).all()
+    # match particles by momentum (unique floats), then compare
+    o1 = np.lexsort((got_m[:, 2], got_m[:, 1], got_m[:, 0]))
+    o2 = np.lexsort((mr[:, 2], mr[:, 1], mr[:, 0]))
+    assert np.abs(got_m[o1] - mr[o2]).max() <= TOL * np.abs(mr).max()
+    d = np.abs(got_p[o1] - pr[o2])
+    d = np.minimum(d, L - d)
+    assert d.max() <= 1e-5 * cfg.cell
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_sharded_power_spectrum(world):
+    from nbody_b200.dist import DistPowerSpectrum, run_threaded
+    from nbody_b200.engine import Engine
+    L, n, N = 1000.0, 16, 32
+    pos = zeldovich_particles(n, L, seed=4)
+    own = owner_np(pos, L, N, world)
+
+    def body(comm):
+        torch.cuda.set_device(0)
+        eng = Engine(0)
+        ps = DistPowerSpectrum(eng, comm, N, L)
+        p = eng.to_device(pos[own == comm.rank])
+        edges, counts, sums = ps(p, pos.shape[0])
+        torch.cuda.synchronize()
+        return counts.cpu().numpy(), sums.cpu().numpy()
+
+    res = run_threaded(world, body)
+    kr, pr, cr = restate.power_spectrum_from_positions(pos, L, N, return_counts=True)
+    for counts, sums in res:
+        assert np.array_equal(counts, cr)                      # bin counts bit-exact on every rank
+        valid = counts > 0
+        assert np.abs(sums[valid] / counts[valid] / pr - 1).max() <= TOL
+
+
+def test_deposit_slab_reports_foreign_particles():
+    from nbody_b200.engine import Engine
+    eng = Engine(0)
+    L, N = 100.0, 16
+    pos = eng.to_device(np.array([[1.0, 2.0, 3.0], [60.0, 2.0, 3.0]]))
+    grid = torch.empty((4 + 2, N, N), dtype=torch.float32, device=eng.device)
+    nout = torch.zeros(1, dtype=torch.int64, device=eng.device)
+    eng.cic_deposit_slab(pos, L / N, N, 0, 4, 2, grid, n_outside=nout)
+    assert int(nout.item()) == 1 and abs(float(grid.sum().item()) - 1.0) < 1e-6
