@@ -132,7 +132,7 @@ extern "C" int nb_cic_deposit_slab(nb_ctx* ctx, const double* pos, int64_t np, d
   NB_REQUIRE(ctx && grid, "ctx/grid is NULL");
   NB_REQUIRE(np >= 0 && (np == 0 || pos), "pos is NULL");
   NB_REQUIRE(N >= 1 && cell > 0.0, "bad N / cell");
-  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && n_ghost >= 0 && nx_own + n_ghost <= N, "bad slab");
+  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && nx_own <= N && n_ghost >= 0, "bad slab");
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   return deposit_launch(ctx, pos, np, cell, N, x0, nx_own + n_ghost, grid, NB_F32, shift, accumulate, nullptr,
                         (unsigned long long*)n_outside, (cudaStream_t)stream);

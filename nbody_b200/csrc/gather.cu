@@ -99,7 +99,7 @@ gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__
                          double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
                          double* __restrict__ acc_out, int64_t np, double gscale, double kick, double drift,
                          double L) {
-  const int64_t n3 = (int64_t)(nxp < N ? nxp : N) * N * N;
+  const int64_t n3 = (int64_t)nxp * N * N;   // component stride of the field buffers
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
     const double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
@@ -200,7 +200,7 @@ extern "C" int nb_gather_kick_drift_slab(nb_ctx* ctx, const float* force3, const
                                          int x0, int nx_own, int n_ghost, double cell, double* pos, double* mom,
                                          double* acc_out, int64_t np, double gscale, double kick, double drift,
                                          double L, void* stream) {
-  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && n_ghost >= 0 && nx_own + n_ghost <= N, "bad slab");
+  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && nx_own <= N && n_ghost >= 0, "bad slab");
   return gkd_launch(ctx, force3, force3_shifted, N, x0, nx_own + n_ghost, cell, pos, mom, acc_out, np, gscale,
                     kick, drift, L, (cudaStream_t)stream);
 }
