@@ -77,16 +77,19 @@ class TorchComm:
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
 
-    def all_to_all(self, out: torch.Tensor, inp: torch.Tensor):
-        """Equal contiguous chunks: out[s-th chunk] = chunk `rank` of rank s's inp."""
+    def all_to_all(self, out: torch.Tensor, inp: torch.Tensor, async_op: bool = False):
+        """Equal contiguous chunks: out[s-th chunk] = chunk `rank` of rank s's inp.  With
+        async_op the exchange runs on the communicator's stream and a handle with .wait() (the
+        current stream waits, the host does not) is returned, so transforms of the next mesh
+        overlap the transpose of this one."""
         if self.world == 1:
             out.view(-1).copy_(inp.view(-1))
-            return out
+            return _DONE if async_op else out
         o, i = out.view(-1), inp.view(-1)
         if o.is_complex():
             o, i = torch.view_as_real(o).view(-1), torch.view_as_real(i).view(-1)
-        self.dist.all_to_all_single(o, i, group=self.group)
-        return out
+        w = self.dist.all_to_all_single(o, i, group=self.group, async_op=async_op)
+        return w if async_op else out
 
     def shift(self, send: torch.Tensor, recv: torch.Tensor, delta: int):
         """send -> rank+delta, recv <- rank-delta (ring)."""
@@ -138,6 +141,14 @@ class TorchComm:
             self.dist.barrier(group=self.group)
 
 
+class _Done:
+    def wait(self):
+        return True
+
+
+_DONE = _Done()
+
+
 class ThreadWorld:
     """Shared state of `world` emulated ranks running as threads of one process."""
 
@@ -164,14 +175,14 @@ class ThreadComm:
     def _done(self):
         self.tw.bar.wait()
 
-    def all_to_all(self, out, inp):
+    def all_to_all(self, out, inp, async_op=False):
         got = self._swap(inp)
         n = out.numel() // self.world
         o = out.view(-1)
         for s in range(self.world):
             o[s * n:(s + 1) * n].copy_(got[s].view(-1)[self.rank * n:(self.rank + 1) * n])
         self._done()
-        return out
+        return _DONE if async_op else out
 
     def shift(self, send, recv, delta):
         got = self._swap(send)
@@ -253,7 +264,9 @@ class SlabMesh:
         self.rho = torch.empty((nb_fwd, npl, N, N), dtype=torch.float32, device=dev)
         self.ghost_rx = torch.empty((nb_fwd, lay.n_ghost, N, N), dtype=torch.float32, device=dev)
         self.s2d = torch.empty((lay.nxl, N, lay.nzh), dtype=torch.complex64, device=dev)
-        self.xbuf = torch.empty((lay.world, lay.nxl, lay.nyl, lay.nzh), dtype=torch.complex64, device=dev)
+        self.xbufs = [torch.empty((lay.world, lay.nxl, lay.nyl, lay.nzh), dtype=torch.complex64, device=dev)
+                      for _ in range(2 if (nb_fwd > 1 or nc_inv > 1) else 1)]
+        self.xbuf = self.xbufs[0]
         self.rhok = torch.empty((nb_fwd, N, lay.nyl, lay.nzh), dtype=torch.complex64, device=dev)
         self.n_outside = torch.zeros(1, dtype=torch.int64, device=dev)
         if nc_inv:
@@ -274,14 +287,43 @@ class SlabMesh:
 
     # real x-slab b -> y-slab spectrum rhok[b]  ([N][nyl][nzh])
     def forward(self, b: int):
-        lay, eng = self.lay, self.eng
-        eng.slab_fft2d(self.N, lay.nxl, +1, self.rho[b], self.s2d)
-        eng.slab_pack(self.s2d, self.xbuf, lay.nxl, lay.world, lay.nyl, lay.nzh)
-        self.comm.all_to_all(self.rhok[b], self.xbuf)
-        eng.slab_fft1d_x(self.N, lay.rows, +1, self.rhok[b])
-        return self.rhok[b]
+        return self.forward_all(1, first=b)[0]
 
-    # y-slab spectrum g[c] -> real x-slab force[c] (first nxl planes)
+    def forward_all(self, nb: int, first: int = 0):
+        """2-D R2C + pack of mesh b+1 overlap the all-to-all of mesh b."""
+        lay, eng = self.lay, self.eng
+        works = []
+        for k in range(nb):
+            b = first + k
+            xb = self.xbufs[k % len(self.xbufs)]
+            eng.slab_fft2d(self.N, lay.nxl, +1, self.rho[b], self.s2d)
+            eng.slab_pack(self.s2d, xb, lay.nxl, lay.world, lay.nyl, lay.nzh)
+            works.append(self.comm.all_to_all(self.rhok[b], xb, async_op=True))
+        for k in range(nb):
+            works[k].wait()
+            eng.slab_fft1d_x(self.N, lay.rows, +1, self.rhok[first + k])
+        return [self.rhok[first + k] for k in range(nb)]
+
+    # y-slab spectra g[0:nc] -> real x-slabs force[0:nc] (first nxl planes)
+    def inverse_all(self, nc: int):
+        """Software pipeline: the x transform of component c+1 and the unpack + 2-D C2R of
+        component c-1 run while the all-to-all of component c is in flight."""
+        lay, eng = self.lay, self.eng
+        works = [None] * nc
+
+        def finish(c):
+            works[c].wait()
+            eng.slab_unpack(self.xbufs[c % len(self.xbufs)], self.s2d, lay.nxl, lay.world, lay.nyl, lay.nzh)
+            eng.slab_fft2d(self.N, lay.nxl, -1, self.force[c], self.s2d)
+
+        for c in range(nc):
+            eng.slab_fft1d_x(self.N, lay.rows, -1, self.g[c])
+            if c >= len(self.xbufs):
+                finish(c - len(self.xbufs))          # frees the exchange buffer this component reuses
+            works[c] = self.comm.all_to_all(self.xbufs[c % len(self.xbufs)], self.g[c], async_op=True)
+        for c in range(max(0, nc - len(self.xbufs)), nc):
+            finish(c)
+
     def inverse(self, c: int):
         lay, eng = self.lay, self.eng
         eng.slab_fft1d_x(self.N, lay.rows, -1, self.g[c])
@@ -335,12 +377,12 @@ class DistForceStepper:
         c, m, mk = self.cfg, self.mesh, self._mark
         N = c.gridsize
         mk("deposit+ghost_add", lambda: m.deposit(pos, self.nb))
-        mk("fft_fwd(2D R2C, pack, all-to-all, 1D)", lambda: [m.forward(b) for b in range(self.nb)])
+        mk("fft_fwd(2D R2C, pack, all-to-all, 1D)", lambda: m.forward_all(self.nb))
         pref = 4.0 * math.pi * c.G * c.mass / c.cell ** 3 / float(N) ** 3
         mk("kspace", lambda: self.eng.kspace_fused_slab(
             m.rhok[0], m.rhok[1] if self.nb == 2 else None, c.boxsize, N, m.lay.y0, m.lay.nyl, c.r_s,
             c.deconv_order, pref, m.g[0:3], m.g[3:6] if self.nc == 6 else None))
-        mk("fft_inv(1D, all-to-all, unpack, 2D C2R)", lambda: [m.inverse(k) for k in range(self.nc)])
+        mk("fft_inv(1D, all-to-all, unpack, 2D C2R)", lambda: m.inverse_all(self.nc))
         mk("force_ghosts", lambda: m.fill_force_ghosts(self.nc))
         return m.force[0:3], (m.force[3:6] if self.nc == 6 else None)
 
@@ -400,21 +442,42 @@ class DistForceStepper:
 
     # -- migration ----------------------------------------------------------------------------------
     def migrate(self, pos, mom):
-        """Hand particles that drifted out of this rank's x-slab to their new owner."""
+        """Hand particles that drifted out of this rank's x-slab to their new owner.  Only the
+        leavers and the arrivals are moved: arrivals fill the leavers' slots, a surplus is
+        appended, a deficit is closed by moving particles from the tail into the open slots."""
         c, lay = self.cfg, self.mesh.lay
         if self.world == 1:
             return pos, mom
+        n = pos.shape[0]
         owner, counts = self.eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world)
-        moved = (pos.shape[0] - counts[self.rank]).reshape(1).clone()
+        moved = (n - counts[self.rank]).reshape(1).clone()
         self.comm.all_reduce(moved, "max")
         if int(moved.item()) == 0:                                  # host sync, once per step
             return pos, mom
-        pm = torch.cat([pos, mom], dim=1)
-        send = [pm[owner == d] if d != self.rank else None for d in range(self.world)]
-        got = self.comm.exchange_var(send)
-        keep = pm[owner == self.rank]
-        pm = torch.cat([keep] + [g for g in got if g.shape[0]])
-        return pm[:, :3].contiguous(), pm[:, 3:].contiguous()
+        out_idx = (owner != self.rank).nonzero().squeeze(1)        # ascending
+        dest = owner[out_idx]
+        leaving = torch.cat([pos[out_idx], mom[out_idx]], dim=1)
+        send = [leaving[dest == d] if d != self.rank else None for d in range(self.world)]
+        got = [g for g in self.comm.exchange_var(send) if g.shape[0]]
+        arrivals = torch.cat(got) if got else leaving.new_empty((0, 6))
+        n_out, n_in = int(out_idx.shape[0]), int(arrivals.shape[0])
+        k = min(n_out, n_in)
+        if k:
+            pos[out_idx[:k]] = arrivals[:k, :3]
+            mom[out_idx[:k]] = arrivals[:k, 3:]
+        if n_in > n_out:
+            pos = torch.cat([pos, arrivals[k:, :3]])
+            mom = torch.cat([mom, arrivals[k:, 3:]])
+        elif n_out > n_in:
+            holes = out_idx[k:]
+            n_new = n - holes.shape[0]
+            tail = torch.arange(n_new, n, device=pos.device)
+            tail_keep = tail[~torch.isin(tail, holes)]
+            low = holes[holes < n_new]
+            pos[low] = pos[tail_keep]
+            mom[low] = mom[tail_keep]
+            pos, mom = pos[:n_new], mom[:n_new]
+        return pos, mom
 
     # -- public ---------------------------------------------------------------------------------------
     def accel(self, pos, n_total: int = 0, periodic_pp=False):
