@@ -347,6 +347,431 @@ p3m_short_v2_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// v3 — "8 i x 4 j-streams, packed pairs" (default).
+//
+// Two things held v1 back (profiles/r1a, r1b): (a) a cell holds ~22 particles at BASELINE
+// config 5, so a warp with one i-particle per lane runs at ~65 % lane occupancy; (b) every
+// candidate costs ~40 scalar issue slots.  v3 changes the lane mapping and the arithmetic:
+//   lanes     lane = 8·s + i: 8 i-particles of the cell (i-blocks of 8: 22 particles -> 3
+//             passes at 92 % occupancy) times 4 j-streams s; the three xor-shuffle levels a
+//             per-i reduction needs shrink to two (over s) once per i-block;
+//   tile      the j-particles of the 27 neighbour cells are copied once per CELL (not per
+//             i-block) into a per-warp SoA shared-memory tile, translated into the frame of
+//             the i-cell, padded with far-away sentinels to a multiple of 8;
+//   pairs     every lane takes TWO consecutive candidates per iteration as one LDS.64 per
+//             coordinate and evaluates them with packed FP32 (add/mul/fma.f32x2 -> FADD2 /
+//             FMUL2 / FFMA2): separation, r², softened r^-3, u = w·rsqrt(w), the degree-10
+//             split polynomial, accumulation — ~21 issue slots per candidate instead of 40;
+//             only the 4 MUFU.RSQ, 2 FSETP and 2 FSEL per pair stay scalar.
+// Coincident points (the self pair) have d = 0 and a finite r^-3 (ε² is clamped to >= 1e-20),
+// so they contribute exactly 0 like the oracle's r > 0 condition.
+// sorted_xyzw.w (the mass) must be uniform: nb_cell_sort writes the scalar `mass` there.
+#define P3M3_WARPS 4
+#define P3M3_CAP 768     // candidate tile capacity per warp (multiple of 8); typical 27-cell load ~620
+
+struct P3m3Packed {
+  p3m_f32x2 eps2, ws, tiny, ts, m1, one, wj;
+  p3m_f32x2 nq[P3M_DEG + 1];   // NEGATED split coefficients: f = 1 + w·u·nQ(t)
+  float rc2;
+};
+
+__device__ __forceinline__ p3m_f32x2 p3m_rsqrt2(p3m_f32x2 v) {
+  float a, b;
+  p3m_unpack2(v, a, b);
+  return p3m_pack2(p3m_rsqrt(a), p3m_rsqrt(b));
+}
+
+// the 8 i-particles of this i-block (lane & 7) against the `npad` (multiple of 8) tile slots
+__device__ __forceinline__ void p3m3_process(const float* __restrict__ tx, const float* __restrict__ ty,
+                                             const float* __restrict__ tz, int npad, int strm, p3m_f32x2 nxi,
+                                             p3m_f32x2 nyi, p3m_f32x2 nzi, const P3m3Packed& k, double& ax,
+                                             double& ay, double& az) {
+  p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull;   // (+0.f, +0.f)
+#pragma unroll 2
+  for (int v = 2 * strm; v < npad; v += 8) {
+    const p3m_f32x2 X = *reinterpret_cast<const p3m_f32x2*>(tx + v);
+    const p3m_f32x2 Y = *reinterpret_cast<const p3m_f32x2*>(ty + v);
+    const p3m_f32x2 Z = *reinterpret_cast<const p3m_f32x2*>(tz + v);
+    const p3m_f32x2 dx = p3m_add2(X, nxi), dy = p3m_add2(Y, nyi), dz = p3m_add2(Z, nzi);
+    p3m_f32x2 r2 = p3m_mul2(dx, dx);
+    r2 = p3m_fma2(dy, dy, r2);
+    r2 = p3m_fma2(dz, dz, r2);
+    float r2a, r2b;
+    p3m_unpack2(r2, r2a, r2b);
+    const bool in0 = r2a < k.rc2, in1 = r2b < k.rc2;
+    const p3m_f32x2 rinv = p3m_rsqrt2(p3m_add2(r2, k.eps2));
+    const p3m_f32x2 w = p3m_mul2(r2, k.ws);                          // u²
+    const p3m_f32x2 u = p3m_mul2(w, p3m_rsqrt2(p3m_add2(w, k.tiny)));
+    const p3m_f32x2 tt = p3m_fma2(w, k.ts, k.m1);
+    p3m_f32x2 q = k.nq[P3M_DEG];
+#pragma unroll
+    for (int d = P3M_DEG - 1; d >= 0; --d) q = p3m_fma2(q, tt, k.nq[d]);
+    const p3m_f32x2 f = p3m_fma2(p3m_mul2(w, u), q, k.one);          // erfc(u) + 2u/sqrt(pi) exp(-u²)
+    const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
+    float s0, s1;
+    p3m_unpack2(s, s0, s1);
+    const p3m_f32x2 sm = p3m_pack2(in0 ? s0 : 0.f, in1 ? s1 : 0.f);
+    FX = p3m_fma2(sm, dx, FX);
+    FY = p3m_fma2(sm, dy, FY);
+    FZ = p3m_fma2(sm, dz, FZ);
+  }
+  float a, b;
+  p3m_unpack2(FX, a, b); ax += (double)(a + b);
+  p3m_unpack2(FY, a, b); ay += (double)(a + b);
+  p3m_unpack2(FZ, a, b); az += (double)(a + b);
+}
+
+__global__ void __launch_bounds__(P3M3_WARPS * 32, 4)
+p3m_short_v3_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                    const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap) {
+  extern __shared__ __align__(16) float p3m3_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int li = lane & 7, strm = lane >> 3;
+  float* tx = p3m3_smem + warp * (3 * cap);   // cap: tile capacity per warp, a multiple of 8
+  float* ty = tx + cap;
+  float* tz = ty + cap;
+  P3m3Packed k;
+  {
+    const float e2 = fmaxf(prm.eps2, 1e-20f);
+    const float wj = __ldg(&sorted[0].w);   // uniform mass (nb_cell_sort)
+    k.eps2 = p3m_pack2(e2, e2);
+    k.ws = p3m_pack2(prm.w_scale, prm.w_scale);
+    k.tiny = p3m_pack2(1e-30f, 1e-30f);
+    k.ts = p3m_pack2(prm.t_scale, prm.t_scale);
+    k.m1 = p3m_pack2(-1.f, -1.f);
+    k.one = p3m_pack2(1.f, 1.f);
+    k.wj = p3m_pack2(wj, wj);
+#pragma unroll
+    for (int d = 0; d <= P3M_DEG; ++d) k.nq[d] = p3m_pack2(-prm.coef[d], -prm.coef[d]);
+    k.rc2 = prm.rc2;
+  }
+  const int64_t wstride = (int64_t)gridDim.x * P3M3_WARPS;
+  for (int64_t c = cell_lo + (int64_t)blockIdx.x * P3M3_WARPS + warp; c < cell_hi; c += wstride) {
+    const int is = cell_start[c], ie = cell_start[c + 1];
+    if (is == ie) continue;
+    const int cz = (int)(c % ncs);
+    const int cy = (int)((c / ncs) % ncs);
+    const int cx = (int)(c / ((int64_t)ncs * ncs));
+    // lanes 0..26 look up the j-ranges of the 27 neighbour cells
+    int my_js = 0, my_je = 0;
+    if (lane < 27) {
+      int nx = cx + lane / 9 - 1, ny = cy + (lane / 3) % 3 - 1, nz = cz + lane % 3 - 1;
+      nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+      ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+      nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+      const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+      my_js = cell_start[n];
+      my_je = cell_start[n + 1];
+    }
+    int ncand = my_je - my_js;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ncand += __shfl_xor_sync(0xffffffffu, ncand, o);
+    const bool single = ncand <= cap;   // whole neighbourhood fits: fill once per cell
+    int resident = 0;                        // padded slot count of the resident tile (0 = not yet filled)
+    for (int ib = is; ib < ie; ib += 8) {
+      const int i = ib + li;
+      // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+      const int oi = i < ie ? perm[i] : 0x7fffffff;
+      const bool ivalid = oi < i_limit;
+      if (!__any_sync(0xffffffffu, ivalid)) continue;
+      const float4 pi = sorted[i < ie ? i : is];
+      const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
+      double ax = 0.0, ay = 0.0, az = 0.0;
+      if (resident) {
+        p3m3_process(tx, ty, tz, resident, strm, nxi, nyi, nzi, k, ax, ay, az);
+      } else {
+        int fill = 0;
+        for (int n = 0; n < 27; ++n) {
+          int js = __shfl_sync(0xffffffffu, my_js, n);
+          const int je = __shfl_sync(0xffffffffu, my_je, n);
+          const float offx = (float)(n / 9 - 1) * prm.cs;
+          const float offy = (float)((n / 3) % 3 - 1) * prm.cs;
+          const float offz = (float)(n % 3 - 1) * prm.cs;
+          while (js < je) {
+            const int take = min(je - js, cap - fill);
+            for (int t = lane; t < take; t += 32) {
+              const float4 p = sorted[js + t];
+              tx[fill + t] = p.x + offx;
+              ty[fill + t] = p.y + offy;
+              tz[fill + t] = p.z + offz;
+            }
+            fill += take;
+            js += take;
+            if (fill == cap) {   // only when !single
+              __syncwarp();
+              p3m3_process(tx, ty, tz, fill, strm, nxi, nyi, nzi, k, ax, ay, az);
+              __syncwarp();
+              fill = 0;
+            }
+          }
+        }
+        const int npad = (fill + 7) & ~7;
+        if (lane < npad - fill) {   // sentinels: far outside any cutoff
+          tx[fill + lane] = 1e18f;
+          ty[fill + lane] = 0.f;
+          tz[fill + lane] = 0.f;
+        }
+        __syncwarp();
+        if (npad > 0) p3m3_process(tx, ty, tz, npad, strm, nxi, nyi, nzi, k, ax, ay, az);
+        __syncwarp();
+        if (single) resident = npad;
+      }
+      // fold the 4 j-streams of each i-particle
+      ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
+      az += __shfl_xor_sync(0xffffffffu, az, 8);
+      ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
+      az += __shfl_xor_sync(0xffffffffu, az, 16);
+      if (ivalid && strm == 0) {
+        const int64_t o = oi;
+        if (accumulate) {
+          acc[3 * o] += ax * scale; acc[3 * o + 1] += ay * scale; acc[3 * o + 2] += az * scale;
+        } else {
+          acc[3 * o] = ax * scale; acc[3 * o + 1] = ay * scale; acc[3 * o + 2] = az * scale;
+        }
+      }
+    }
+    __syncwarp();   // the next cell overwrites the tile
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// v4 — v3's lane mapping with a two-phase pair loop: test all, evaluate in-range only.
+//
+// ncu on v3 (profiles/r1d_*): the FMA pipe is the limiter (63 % active) and 29 of its lane-ops
+// per candidate are spent on pairs of which only 16 % are inside r_cut.  v4 keeps the tile and
+// the 8 i x 4 j-stream mapping and splits the loop:
+//   fill      the candidates of the 27 neighbour cells form ONE flattened list (exclusive
+//             prefix of the 27 cell populations by warp shuffle, kept in shared memory);
+//             lane t loads candidate t, t+32, ... after a 5-step binary search for its cell —
+//             independent loads (the v3 fill ran 27 dependent load->store rounds per cell);
+//   phase 1   per lane and iteration TWO candidates: 3 LDS.64, 6 packed FP32 ops for r², two
+//             compares; an in-range candidate's tile index (u16) is pushed on the lane's
+//             PRIVATE queue column in shared memory — no ballot, no prefix, no atomics;
+//   phase 2   when any lane's queue is nearly full, and at the end of the i-block: every lane
+//             pops two entries per round, re-reads the two j-particles from the tile and runs
+//             the packed evaluation of v3 (rounds = max over lanes of its hit count / 2);
+// so the expensive part runs ~6x less often.  Queue columns are lane-private (bank = lane/2,
+// u16 entries), stale entries beyond a lane's count are valid tile indices and are masked.
+#define P3M4_WARPS 4
+#define P3M4_QD 64       // queue depth per lane (entries); drained when a lane exceeds QD - 16
+#define P3M4_CAP 768     // tile capacity per warp (candidates; multiple of 8)
+
+// per-warp shared memory: tile (3·cap floats), run table (2·32 ints), queue (QD·32 u16)
+__host__ __device__ inline size_t p3m4_warp_bytes(int cap) {
+  return sizeof(float) * 3 * (size_t)cap + sizeof(int) * 64 + sizeof(unsigned short) * P3M4_QD * 32;
+}
+
+// Load the flattened candidates [first, first + nt) into tile slots [0, nt), translated into
+// the frame of the i-cell, and pad with far-away sentinels to a multiple of 8.
+__device__ __forceinline__ void p3m4_fill(const float4* __restrict__ sorted, const int* __restrict__ roff,
+                                          const int* __restrict__ rjs, const float* __restrict__ offtab,
+                                          float* __restrict__ tx, float* __restrict__ ty, float* __restrict__ tz,
+                                          int first, int nt, int lane) {
+#pragma unroll 2
+  for (int t = lane; t < nt; t += 32) {
+    const int g = first + t;
+    int n = 0;   // largest n with roff[n] <= g  (roff[27..31] = INT_MAX)
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) n = (roff[n + s] <= g) ? n + s : n;
+    const float4 p = sorted[rjs[n] + (g - roff[n])];
+    tx[t] = p.x + offtab[3 * n];
+    ty[t] = p.y + offtab[3 * n + 1];
+    tz[t] = p.z + offtab[3 * n + 2];
+  }
+  const int npad = (nt + 7) & ~7;
+  if (lane < npad - nt) {
+    tx[nt + lane] = 1e18f;
+    ty[nt + lane] = 0.f;
+    tz[nt + lane] = 0.f;
+  }
+  __syncwarp();
+}
+
+// phase 2: evaluate the queued candidates of every lane, two per round
+__device__ __forceinline__ void p3m4_drain(const float* __restrict__ tx, const float* __restrict__ ty,
+                                           const float* __restrict__ tz, const unsigned short* __restrict__ qcol,
+                                           int cnt, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
+                                           const P3m3Packed& k, double& ax, double& ay, double& az) {
+  const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 1) >> 1;
+  p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull;
+#pragma unroll 2
+  for (int r = 0; r < rounds; ++r) {
+    const int v0 = qcol[(2 * r) * 32], v1 = qcol[(2 * r + 1) * 32];
+    const bool ok0 = 2 * r < cnt, ok1 = 2 * r + 1 < cnt;
+    const p3m_f32x2 dx = p3m_add2(p3m_pack2(tx[v0], tx[v1]), nxi);
+    const p3m_f32x2 dy = p3m_add2(p3m_pack2(ty[v0], ty[v1]), nyi);
+    const p3m_f32x2 dz = p3m_add2(p3m_pack2(tz[v0], tz[v1]), nzi);
+    p3m_f32x2 r2 = p3m_mul2(dx, dx);
+    r2 = p3m_fma2(dy, dy, r2);
+    r2 = p3m_fma2(dz, dz, r2);
+    const p3m_f32x2 rinv = p3m_rsqrt2(p3m_add2(r2, k.eps2));
+    const p3m_f32x2 w = p3m_mul2(r2, k.ws);                          // u²
+    const p3m_f32x2 u = p3m_mul2(w, p3m_rsqrt2(p3m_add2(w, k.tiny)));
+    const p3m_f32x2 tt = p3m_fma2(w, k.ts, k.m1);
+    p3m_f32x2 q = k.nq[P3M_DEG];
+#pragma unroll
+    for (int d = P3M_DEG - 1; d >= 0; --d) q = p3m_fma2(q, tt, k.nq[d]);
+    const p3m_f32x2 f = p3m_fma2(p3m_mul2(w, u), q, k.one);          // erfc(u) + 2u/sqrt(pi) exp(-u²)
+    const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
+    float s0, s1;
+    p3m_unpack2(s, s0, s1);
+    const p3m_f32x2 sm = p3m_pack2(ok0 ? s0 : 0.f, ok1 ? s1 : 0.f);
+    FX = p3m_fma2(sm, dx, FX);
+    FY = p3m_fma2(sm, dy, FY);
+    FZ = p3m_fma2(sm, dz, FZ);
+  }
+  float a, b;
+  p3m_unpack2(FX, a, b); ax += (double)(a + b);
+  p3m_unpack2(FY, a, b); ay += (double)(a + b);
+  p3m_unpack2(FZ, a, b); az += (double)(a + b);
+}
+
+// phase 1 over the resident tile slots [0, npad); drains when a queue runs full and at the end
+__device__ __forceinline__ void p3m4_pass(const float* __restrict__ tx, const float* __restrict__ ty,
+                                          const float* __restrict__ tz, unsigned short* __restrict__ qcol,
+                                          int npad, int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
+                                          const P3m3Packed& k, double& ax, double& ay, double& az) {
+  int cnt = 0;
+  for (int vb = 0; vb < npad; vb += 64) {
+    const int vend = min(vb + 64, npad);
+#pragma unroll 4
+    for (int v = vb + 2 * strm; v < vend; v += 8) {
+      const p3m_f32x2 X = *reinterpret_cast<const p3m_f32x2*>(tx + v);
+      const p3m_f32x2 Y = *reinterpret_cast<const p3m_f32x2*>(ty + v);
+      const p3m_f32x2 Z = *reinterpret_cast<const p3m_f32x2*>(tz + v);
+      const p3m_f32x2 dx = p3m_add2(X, nxi), dy = p3m_add2(Y, nyi), dz = p3m_add2(Z, nzi);
+      p3m_f32x2 r2 = p3m_mul2(dx, dx);
+      r2 = p3m_fma2(dy, dy, r2);
+      r2 = p3m_fma2(dz, dz, r2);
+      float r2a, r2b;
+      p3m_unpack2(r2, r2a, r2b);
+      if (r2a < k.rc2) { qcol[cnt * 32] = (unsigned short)v; ++cnt; }
+      if (r2b < k.rc2) { qcol[cnt * 32] = (unsigned short)(v + 1); ++cnt; }
+    }
+    if (__any_sync(0xffffffffu, cnt > P3M4_QD - 16)) {
+      __syncwarp();
+      p3m4_drain(tx, ty, tz, qcol, cnt, nxi, nyi, nzi, k, ax, ay, az);
+      cnt = 0;
+    }
+  }
+  if (__any_sync(0xffffffffu, cnt > 0)) {
+    __syncwarp();
+    p3m4_drain(tx, ty, tz, qcol, cnt, nxi, nyi, nzi, k, ax, ay, az);
+  }
+}
+
+template <bool QUEUE>
+__global__ void __launch_bounds__(P3M4_WARPS * 32, 4)
+p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                    const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap) {
+  extern __shared__ __align__(16) unsigned char p3m4_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int li = lane & 7, strm = lane >> 3;
+  // CTA-wide: translation of neighbour n = (ox+1)*9 + (oy+1)*3 + (oz+1) into the i-cell frame
+  float* offtab = reinterpret_cast<float*>(p3m4_smem);                       // 27*3 floats (96 reserved)
+  unsigned char* wbase = p3m4_smem + 96 * sizeof(float) + (size_t)warp * p3m4_warp_bytes(cap);
+  float* tx = reinterpret_cast<float*>(wbase);
+  float* ty = tx + cap;
+  float* tz = ty + cap;
+  int* roff = reinterpret_cast<int*>(tz + cap);                               // 32: exclusive prefix
+  int* rjs = roff + 32;                                                       // 32: first slot of the cell
+  unsigned short* qcol = reinterpret_cast<unsigned short*>(rjs + 32) + lane;  // this lane's queue column
+  if (threadIdx.x < 27) {
+    const int n = threadIdx.x;
+    offtab[3 * n] = (float)(n / 9 - 1) * prm.cs;
+    offtab[3 * n + 1] = (float)((n / 3) % 3 - 1) * prm.cs;
+    offtab[3 * n + 2] = (float)(n % 3 - 1) * prm.cs;
+  }
+  for (int r = 0; r < P3M4_QD; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
+  __syncthreads();
+  P3m3Packed k;
+  {
+    const float e2 = fmaxf(prm.eps2, 1e-20f);
+    const float wj = __ldg(&sorted[0].w);   // uniform mass (nb_cell_sort)
+    k.eps2 = p3m_pack2(e2, e2);
+    k.ws = p3m_pack2(prm.w_scale, prm.w_scale);
+    k.tiny = p3m_pack2(1e-30f, 1e-30f);
+    k.ts = p3m_pack2(prm.t_scale, prm.t_scale);
+    k.m1 = p3m_pack2(-1.f, -1.f);
+    k.one = p3m_pack2(1.f, 1.f);
+    k.wj = p3m_pack2(wj, wj);
+#pragma unroll
+    for (int d = 0; d <= P3M_DEG; ++d) k.nq[d] = p3m_pack2(-prm.coef[d], -prm.coef[d]);
+    k.rc2 = prm.rc2;
+  }
+  const int64_t wstride = (int64_t)gridDim.x * P3M4_WARPS;
+  for (int64_t c = cell_lo + (int64_t)blockIdx.x * P3M4_WARPS + warp; c < cell_hi; c += wstride) {
+    const int is = cell_start[c], ie = cell_start[c + 1];
+    if (is == ie) continue;
+    const int cz = (int)(c % ncs);
+    const int cy = (int)((c / ncs) % ncs);
+    const int cx = (int)(c / ((int64_t)ncs * ncs));
+    // lanes 0..26: population of the 27 neighbour cells, then their exclusive prefix
+    int my_js = 0, my_len = 0;
+    if (lane < 27) {
+      int nx = cx + lane / 9 - 1, ny = cy + (lane / 3) % 3 - 1, nz = cz + lane % 3 - 1;
+      nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+      ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+      nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+      const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+      my_js = cell_start[n];
+      my_len = cell_start[n + 1] - my_js;
+    }
+    int incl = my_len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    const int ncand = __shfl_sync(0xffffffffu, incl, 31);
+    __syncwarp();   // the previous cell's fills are done with the run table
+    roff[lane] = lane < 27 ? incl - my_len : 0x7fffffff;
+    rjs[lane] = my_js;
+    __syncwarp();
+    const bool single = ncand <= cap;   // whole neighbourhood fits: fill once per cell
+    bool resident = false;
+    for (int ib = is; ib < ie; ib += 8) {
+      const int i = ib + li;
+      // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+      const int oi = i < ie ? perm[i] : 0x7fffffff;
+      const bool ivalid = oi < i_limit;
+      if (!__any_sync(0xffffffffu, ivalid)) continue;
+      float4 pi = sorted[i < ie ? i : is];
+      if (!ivalid) pi.x = 3e18f;   // idle lanes never pass the range test (no queue traffic)
+      const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
+      double ax = 0.0, ay = 0.0, az = 0.0;
+      for (int first = 0; first < ncand; first += cap) {
+        const int nt = min(cap, ncand - first);
+        if (!resident) {
+          __syncwarp();   // every lane is done reading the previous chunk
+          p3m4_fill(sorted, roff, rjs, offtab, tx, ty, tz, first, nt, lane);
+        }
+        if constexpr (QUEUE)
+          p3m4_pass(tx, ty, tz, qcol, (nt + 7) & ~7, strm, nxi, nyi, nzi, k, ax, ay, az);
+        else   // v3's evaluate-all loop on the v4 tile (A/B: NB_P3M_KERNEL=5)
+          p3m3_process(tx, ty, tz, (nt + 7) & ~7, strm, nxi, nyi, nzi, k, ax, ay, az);
+      }
+      resident = single;
+      // fold the 4 j-streams of each i-particle
+      ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
+      az += __shfl_xor_sync(0xffffffffu, az, 8);
+      ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
+      az += __shfl_xor_sync(0xffffffffu, az, 16);
+      if (ivalid && strm == 0) {
+        const int64_t o = oi;
+        if (accumulate) {
+          acc[3 * o] += ax * scale; acc[3 * o + 1] += ay * scale; acc[3 * o + 2] += az * scale;
+        } else {
+          acc[3 * o] = ax * scale; acc[3 * o + 1] = ay * scale; acc[3 * o + 2] = az * scale;
+        }
+      }
+    }
+  }
+}
+
 // coef_host: P3M_DEG+1 doubles (monomial coefficients of Q in t, low to high), HOST pointer.
 extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
                             int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
@@ -372,21 +797,47 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   const int ilim = (i_limit <= 0 || i_limit > 0x7fffffff) ? 0x7fffffff : (int)i_limit;
   const int64_t ncell = cell_hi - cell_lo;
   const int64_t cap = (int64_t)ctx->num_sms * 64;
-  // v1 (warp-per-cell, lanes over i) is the default: 138.6 ms at BASELINE config 5 against
-  // 160.6 ms for v2 (profiles/r1b_*).  NB_P3M_KERNEL=2 selects v2 for A/B measurements.
-  static const int use_v1 = [] { const char* e = getenv("NB_P3M_KERNEL"); return !(e && atoi(e) == 2); }();
-  if (use_v1) {
+  // v4 (two-phase: test all, evaluate in-range only) is the default; NB_P3M_KERNEL selects the
+  // older kernels for A/B measurements: 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
+  // compaction, 3 = v3 packed evaluate-all, 5 = v3's loop on v4's flattened tile fill.
+  static const int which = [] { const char* e = getenv("NB_P3M_KERNEL"); const int v = e ? atoi(e) : 4;
+                                return (v >= 1 && v <= 5) ? v : 4; }();
+  if (which == 1) {
     int64_t nblk = (ncell + P3M_WARPS - 1) / P3M_WARPS;
     if (nblk > cap) nblk = cap;
     p3m_short_kernel<<<(int)nblk, P3M_WARPS * 32, 0, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo,
                                                            cell_hi, prm, scale, acc, accumulate, ilim);
-  } else {
+  } else if (which == 2) {
     const size_t smem = sizeof(float) * P3M2_WARPS * P3M2_FLOATS_PER_WARP;
     NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t nblk = (ncell + P3M2_WARPS - 1) / P3M2_WARPS;
     if (nblk > cap) nblk = cap;
     p3m_short_v2_kernel<<<(int)nblk, P3M2_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
                                                                   cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
+  } else if (which == 4 || which == 5) {
+    static const int tile_cap = [] { const char* e = getenv("NB_P3M_CAP"); const int v = e ? atoi(e) : P3M4_CAP;
+                                     return (v >= 64 && v <= 4096) ? (v & ~7) : P3M4_CAP; }();
+    const size_t smem = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap);
+    int64_t nblk = (ncell + P3M4_WARPS - 1) / P3M4_WARPS;
+    if (nblk > cap) nblk = cap;
+    if (which == 4) {
+      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      p3m_short_v4_kernel<true><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>(
+          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, tile_cap);
+    } else {
+      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      p3m_short_v4_kernel<false><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>(
+          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, tile_cap);
+    }
+  } else {
+    static const int tile_cap = [] { const char* e = getenv("NB_P3M_CAP"); const int v = e ? atoi(e) : P3M3_CAP;
+                                     return (v >= 64 && v <= 4096) ? (v & ~7) : P3M3_CAP; }();
+    const size_t smem = sizeof(float) * P3M3_WARPS * 3 * tile_cap;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t nblk = (ncell + P3M3_WARPS - 1) / P3M3_WARPS;
+    if (nblk > cap) nblk = cap;
+    p3m_short_v3_kernel<<<(int)nblk, P3M3_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
+                                                                  cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, tile_cap);
   }
   NB_LAUNCHED(ctx);
   return NB_OK;
