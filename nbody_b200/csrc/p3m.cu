@@ -556,31 +556,45 @@ p3m_short_v3_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
 // u16 entries), stale entries beyond a lane's count are valid tile indices and are masked.
 #define P3M4_WARPS 4
 #define P3M4_QD 64       // queue depth per lane (entries); drained when a lane exceeds QD - 16
-#define P3M4_CAP 768     // tile capacity per warp (candidates; multiple of 8)
+#define P3M4_CAP 768     // tile capacity per warp (candidates; multiple of 32)
 
 // per-warp shared memory: tile (3·cap floats), run table (2·32 ints), queue (QD·32 u16)
-__host__ __device__ inline size_t p3m4_warp_bytes(int cap) {
-  return sizeof(float) * 3 * (size_t)cap + sizeof(int) * 64 + sizeof(unsigned short) * P3M4_QD * 32;
+__host__ __device__ inline size_t p3m4_warp_bytes(int cap, int qd) {
+  return sizeof(float) * 3 * (size_t)cap + sizeof(int) * 64 + sizeof(unsigned short) * (size_t)(qd + 4) * 32;
 }
 
 // Load the flattened candidates [first, first + nt) into tile slots [0, nt), translated into
-// the frame of the i-cell, and pad with far-away sentinels to a multiple of 8.
+// the frame of the i-cell, and pad with far-away sentinels to a multiple of 32 (one group of
+// phase 1).  Four rounds of 32 candidates are handled together so that their binary searches
+// and global loads overlap (no early exit between them: out-of-range lanes re-load the last
+// candidate and skip the store).
 __device__ __forceinline__ void p3m4_fill(const float4* __restrict__ sorted, const int* __restrict__ roff,
                                           const int* __restrict__ rjs, const float* __restrict__ offtab,
                                           float* __restrict__ tx, float* __restrict__ ty, float* __restrict__ tz,
                                           int first, int nt, int lane) {
-#pragma unroll 2
-  for (int t = lane; t < nt; t += 32) {
-    const int g = first + t;
-    int n = 0;   // largest n with roff[n] <= g  (roff[27..31] = INT_MAX)
+  for (int t0 = lane; t0 < nt + lane; t0 += 128) {   // warp-uniform trip count
+    int n[4];
+    float4 p[4];
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) n = (roff[n + s] <= g) ? n + s : n;
-    const float4 p = sorted[rjs[n] + (g - roff[n])];
-    tx[t] = p.x + offtab[3 * n];
-    ty[t] = p.y + offtab[3 * n + 1];
-    tz[t] = p.z + offtab[3 * n + 2];
+    for (int j = 0; j < 4; ++j) {
+      const int g = first + min(t0 + 32 * j, nt - 1);
+      int m = 0;   // largest m with roff[m] <= g  (roff[27..31] = INT_MAX)
+#pragma unroll
+      for (int s = 16; s > 0; s >>= 1) m = (roff[m + s] <= g) ? m + s : m;
+      n[j] = m;
+      p[j] = sorted[rjs[m] + (g - roff[m])];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = t0 + 32 * j;
+      if (t < nt) {
+        tx[t] = p[j].x + offtab[3 * n[j]];
+        ty[t] = p[j].y + offtab[3 * n[j] + 1];
+        tz[t] = p[j].z + offtab[3 * n[j] + 2];
+      }
+    }
   }
-  const int npad = (nt + 7) & ~7;
+  const int npad = (nt + 31) & ~31;
   if (lane < npad - nt) {
     tx[nt + lane] = 1e18f;
     ty[nt + lane] = 0.f;
@@ -589,81 +603,93 @@ __device__ __forceinline__ void p3m4_fill(const float4* __restrict__ sorted, con
   __syncwarp();
 }
 
-// phase 2: evaluate the queued candidates of every lane, two per round
+// one packed evaluation of two queued candidates (tile slots v0, v1; ok = entry is live)
+__device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const float* __restrict__ ty,
+                                           const float* __restrict__ tz, int v0, int v1, bool ok0, bool ok1,
+                                           p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi, const P3m3Packed& k,
+                                           p3m_f32x2& FX, p3m_f32x2& FY, p3m_f32x2& FZ) {
+  const p3m_f32x2 dx = p3m_add2(p3m_pack2(tx[v0], tx[v1]), nxi);
+  const p3m_f32x2 dy = p3m_add2(p3m_pack2(ty[v0], ty[v1]), nyi);
+  const p3m_f32x2 dz = p3m_add2(p3m_pack2(tz[v0], tz[v1]), nzi);
+  p3m_f32x2 r2 = p3m_mul2(dx, dx);
+  r2 = p3m_fma2(dy, dy, r2);
+  r2 = p3m_fma2(dz, dz, r2);
+  const p3m_f32x2 rinv = p3m_rsqrt2(p3m_add2(r2, k.eps2));
+  const p3m_f32x2 w = p3m_mul2(r2, k.ws);                          // u²
+  const p3m_f32x2 u = p3m_mul2(w, p3m_rsqrt2(p3m_add2(w, k.tiny)));
+  const p3m_f32x2 tt = p3m_fma2(w, k.ts, k.m1);
+  p3m_f32x2 q = k.nq[P3M_DEG];
+#pragma unroll
+  for (int d = P3M_DEG - 1; d >= 0; --d) q = p3m_fma2(q, tt, k.nq[d]);
+  const p3m_f32x2 f = p3m_fma2(p3m_mul2(w, u), q, k.one);          // erfc(u) + 2u/sqrt(pi) exp(-u²)
+  const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
+  float s0, s1;
+  p3m_unpack2(s, s0, s1);
+  const p3m_f32x2 sm = p3m_pack2(ok0 ? s0 : 0.f, ok1 ? s1 : 0.f);
+  FX = p3m_fma2(sm, dx, FX);
+  FY = p3m_fma2(sm, dy, FY);
+  FZ = p3m_fma2(sm, dz, FZ);
+}
+
+// phase 2: evaluate the queued candidates of every lane, four per round as two independent
+// packed chains (the queue has 4 rows of slack beyond QD, so reading ahead is always in range)
 __device__ __forceinline__ void p3m4_drain(const float* __restrict__ tx, const float* __restrict__ ty,
                                            const float* __restrict__ tz, const unsigned short* __restrict__ qcol,
                                            int cnt, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
                                            const P3m3Packed& k, double& ax, double& ay, double& az) {
-  const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 1) >> 1;
-  p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull;
-#pragma unroll 2
+  const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
+  p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull, GX = 0ull, GY = 0ull, GZ = 0ull;
   for (int r = 0; r < rounds; ++r) {
-    const int v0 = qcol[(2 * r) * 32], v1 = qcol[(2 * r + 1) * 32];
-    const bool ok0 = 2 * r < cnt, ok1 = 2 * r + 1 < cnt;
-    const p3m_f32x2 dx = p3m_add2(p3m_pack2(tx[v0], tx[v1]), nxi);
-    const p3m_f32x2 dy = p3m_add2(p3m_pack2(ty[v0], ty[v1]), nyi);
-    const p3m_f32x2 dz = p3m_add2(p3m_pack2(tz[v0], tz[v1]), nzi);
-    p3m_f32x2 r2 = p3m_mul2(dx, dx);
-    r2 = p3m_fma2(dy, dy, r2);
-    r2 = p3m_fma2(dz, dz, r2);
-    const p3m_f32x2 rinv = p3m_rsqrt2(p3m_add2(r2, k.eps2));
-    const p3m_f32x2 w = p3m_mul2(r2, k.ws);                          // u²
-    const p3m_f32x2 u = p3m_mul2(w, p3m_rsqrt2(p3m_add2(w, k.tiny)));
-    const p3m_f32x2 tt = p3m_fma2(w, k.ts, k.m1);
-    p3m_f32x2 q = k.nq[P3M_DEG];
-#pragma unroll
-    for (int d = P3M_DEG - 1; d >= 0; --d) q = p3m_fma2(q, tt, k.nq[d]);
-    const p3m_f32x2 f = p3m_fma2(p3m_mul2(w, u), q, k.one);          // erfc(u) + 2u/sqrt(pi) exp(-u²)
-    const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
-    float s0, s1;
-    p3m_unpack2(s, s0, s1);
-    const p3m_f32x2 sm = p3m_pack2(ok0 ? s0 : 0.f, ok1 ? s1 : 0.f);
-    FX = p3m_fma2(sm, dx, FX);
-    FY = p3m_fma2(sm, dy, FY);
-    FZ = p3m_fma2(sm, dz, FZ);
+    const int e = 4 * r;
+    const int v0 = qcol[e * 32], v1 = qcol[(e + 1) * 32], v2 = qcol[(e + 2) * 32], v3 = qcol[(e + 3) * 32];
+    p3m4_eval2(tx, ty, tz, v0, v1, e < cnt, e + 1 < cnt, nxi, nyi, nzi, k, FX, FY, FZ);
+    p3m4_eval2(tx, ty, tz, v2, v3, e + 2 < cnt, e + 3 < cnt, nxi, nyi, nzi, k, GX, GY, GZ);
   }
-  float a, b;
-  p3m_unpack2(FX, a, b); ax += (double)(a + b);
-  p3m_unpack2(FY, a, b); ay += (double)(a + b);
-  p3m_unpack2(FZ, a, b); az += (double)(a + b);
+  float a, b, c, d;
+  p3m_unpack2(FX, a, b); p3m_unpack2(GX, c, d); ax += (double)((a + b) + (c + d));
+  p3m_unpack2(FY, a, b); p3m_unpack2(GY, c, d); ay += (double)((a + b) + (c + d));
+  p3m_unpack2(FZ, a, b); p3m_unpack2(GZ, c, d); az += (double)((a + b) + (c + d));
 }
 
-// phase 1 over the resident tile slots [0, npad); drains when a queue runs full and at the end
+// phase 1 over the resident tile slots [0, npad), npad a multiple of 32; drains when a queue
+// runs full and at the end.  One group = 4 iterations of 2 candidates per lane, written out so
+// that the 12 LDS.64 and the four r² chains of a group are independent.
+template <int QD>
 __device__ __forceinline__ void p3m4_pass(const float* __restrict__ tx, const float* __restrict__ ty,
                                           const float* __restrict__ tz, unsigned short* __restrict__ qcol,
                                           int npad, int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
                                           const P3m3Packed& k, double& ax, double& ay, double& az) {
   int cnt = 0;
-  for (int vb = 0; vb < npad; vb += 64) {
-    const int vend = min(vb + 64, npad);
-#pragma unroll 4
-    for (int v = vb + 2 * strm; v < vend; v += 8) {
+  for (int vb = 2 * strm; vb < npad; vb += 32) {
+    p3m_f32x2 r2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int v = vb + 8 * j;
       const p3m_f32x2 X = *reinterpret_cast<const p3m_f32x2*>(tx + v);
       const p3m_f32x2 Y = *reinterpret_cast<const p3m_f32x2*>(ty + v);
       const p3m_f32x2 Z = *reinterpret_cast<const p3m_f32x2*>(tz + v);
       const p3m_f32x2 dx = p3m_add2(X, nxi), dy = p3m_add2(Y, nyi), dz = p3m_add2(Z, nzi);
-      p3m_f32x2 r2 = p3m_mul2(dx, dx);
-      r2 = p3m_fma2(dy, dy, r2);
-      r2 = p3m_fma2(dz, dz, r2);
+      r2[j] = p3m_fma2(dz, dz, p3m_fma2(dy, dy, p3m_mul2(dx, dx)));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int v = vb + 8 * j;
       float r2a, r2b;
-      p3m_unpack2(r2, r2a, r2b);
+      p3m_unpack2(r2[j], r2a, r2b);
       if (r2a < k.rc2) { qcol[cnt * 32] = (unsigned short)v; ++cnt; }
       if (r2b < k.rc2) { qcol[cnt * 32] = (unsigned short)(v + 1); ++cnt; }
     }
-    if (__any_sync(0xffffffffu, cnt > P3M4_QD - 16)) {
-      __syncwarp();
+    // a group pushes at most 8 entries per lane
+    if (__any_sync(0xffffffffu, cnt > QD - 8)) {
       p3m4_drain(tx, ty, tz, qcol, cnt, nxi, nyi, nzi, k, ax, ay, az);
       cnt = 0;
     }
   }
-  if (__any_sync(0xffffffffu, cnt > 0)) {
-    __syncwarp();
-    p3m4_drain(tx, ty, tz, qcol, cnt, nxi, nyi, nzi, k, ax, ay, az);
-  }
+  if (__any_sync(0xffffffffu, cnt > 0)) p3m4_drain(tx, ty, tz, qcol, cnt, nxi, nyi, nzi, k, ax, ay, az);
 }
 
-template <bool QUEUE>
-__global__ void __launch_bounds__(P3M4_WARPS * 32, 4)
+template <bool QUEUE, int QD>
+__global__ void __launch_bounds__(P3M4_WARPS * 32, QD >= 64 ? 4 : 5)
 p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap) {
@@ -672,7 +698,7 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   const int li = lane & 7, strm = lane >> 3;
   // CTA-wide: translation of neighbour n = (ox+1)*9 + (oy+1)*3 + (oz+1) into the i-cell frame
   float* offtab = reinterpret_cast<float*>(p3m4_smem);                       // 27*3 floats (96 reserved)
-  unsigned char* wbase = p3m4_smem + 96 * sizeof(float) + (size_t)warp * p3m4_warp_bytes(cap);
+  unsigned char* wbase = p3m4_smem + 96 * sizeof(float) + (size_t)warp * p3m4_warp_bytes(cap, QD);
   float* tx = reinterpret_cast<float*>(wbase);
   float* ty = tx + cap;
   float* tz = ty + cap;
@@ -685,7 +711,7 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
     offtab[3 * n + 1] = (float)((n / 3) % 3 - 1) * prm.cs;
     offtab[3 * n + 2] = (float)(n % 3 - 1) * prm.cs;
   }
-  for (int r = 0; r < P3M4_QD; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
+  for (int r = 0; r < QD + 4; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
   __syncthreads();
   P3m3Packed k;
   {
@@ -750,9 +776,9 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
           p3m4_fill(sorted, roff, rjs, offtab, tx, ty, tz, first, nt, lane);
         }
         if constexpr (QUEUE)
-          p3m4_pass(tx, ty, tz, qcol, (nt + 7) & ~7, strm, nxi, nyi, nzi, k, ax, ay, az);
+          p3m4_pass<QD>(tx, ty, tz, qcol, (nt + 31) & ~31, strm, nxi, nyi, nzi, k, ax, ay, az);
         else   // v3's evaluate-all loop on the v4 tile (A/B: NB_P3M_KERNEL=5)
-          p3m3_process(tx, ty, tz, (nt + 7) & ~7, strm, nxi, nyi, nzi, k, ax, ay, az);
+          p3m3_process(tx, ty, tz, (nt + 31) & ~31, strm, nxi, nyi, nzi, k, ax, ay, az);
       }
       resident = single;
       // fold the 4 j-streams of each i-particle
@@ -815,20 +841,26 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     p3m_short_v2_kernel<<<(int)nblk, P3M2_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
                                                                   cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
   } else if (which == 4 || which == 5) {
-    static const int tile_cap = [] { const char* e = getenv("NB_P3M_CAP"); const int v = e ? atoi(e) : P3M4_CAP;
-                                     return (v >= 64 && v <= 4096) ? (v & ~7) : P3M4_CAP; }();
-    const size_t smem = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap);
+    // default: queue depth 64, tile 768, 4 CTAs/SM; NB_P3M_QD=32: depth 32, tile 704, 5 CTAs/SM
+    static const int qd = [] { const char* e = getenv("NB_P3M_QD"); return (e && atoi(e) == 32) ? 32 : 64; }();
+    static const int tile_cap = [] { const char* e = getenv("NB_P3M_CAP"); const int d = qd == 64 ? P3M4_CAP : 704;
+                                     const int v = e ? atoi(e) : d; return (v >= 64 && v <= 4096) ? (v & ~31) : d; }();
+    const size_t smem = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, qd);
     int64_t nblk = (ncell + P3M4_WARPS - 1) / P3M4_WARPS;
     if (nblk > cap) nblk = cap;
-    if (which == 4) {
-      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      p3m_short_v4_kernel<true><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>(
-          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, tile_cap);
-    } else {
-      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      p3m_short_v4_kernel<false><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>(
-          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, tile_cap);
-    }
+#define P3M4_LAUNCH(Q, D)                                                                                            \
+  do {                                                                                                               \
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<Q, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
+                                       (int)smem));                                                                  \
+    p3m_short_v4_kernel<Q, D><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, \
+                                                                        ncs, cell_lo, cell_hi, prm, scale, acc,      \
+                                                                        accumulate, ilim, tile_cap);                 \
+  } while (0)
+    if (which == 4 && qd == 64) P3M4_LAUNCH(true, 64);
+    else if (which == 4) P3M4_LAUNCH(true, 32);
+    else if (qd == 64) P3M4_LAUNCH(false, 64);
+    else P3M4_LAUNCH(false, 32);
+#undef P3M4_LAUNCH
   } else {
     static const int tile_cap = [] { const char* e = getenv("NB_P3M_CAP"); const int v = e ? atoi(e) : P3M3_CAP;
                                      return (v >= 64 && v <= 4096) ? (v & ~7) : P3M3_CAP; }();
