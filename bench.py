@@ -502,17 +502,13 @@ def e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work
     torch.cuda.synchronize()
 
     def host_step():
-        pos.copy_(hpos, non_blocking=True)
-        if method != "pk":
-            mom.copy_(hmom, non_blocking=True)
-        r = one_step()
         if method == "pk":
-            _e, counts, sums = r
+            pos.copy_(hpos, non_blocking=True)
+            _e, counts, sums = one_step()
             hout[:299].copy_(counts.to(torch.float64), non_blocking=True)
             hout[299:].copy_(sums, non_blocking=True)
-        else:
-            opos.copy_(pos, non_blocking=True)
-            omom.copy_(mom, non_blocking=True)
+        else:   # the public host-buffer step (mom upload overlapped with the force computation)
+            stepper.step_host(hpos, hmom, opos, omom, 1e-3, 1e-3)
 
     host_step()
     torch.cuda.synchronize()
@@ -525,7 +521,9 @@ def e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work
     ms = a.elapsed_time(b) / steps
     return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
             "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-            "api": "nbody_b200.force.ForceStepper.step on pinned host pos/mom (numpy-level force_step path)"}
+            "api": ("nbody_b200.force.ForceStepper.step_host on pinned host pos/mom (H2D pos, mom upload overlapped "
+                    "with the force computation, D2H pos+mom)" if method != "pk" else
+                    "deposit + overdensity + power_spectrum_bins on pinned host positions, (count,sum) bins back")}
 
 
 def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier):

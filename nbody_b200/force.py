@@ -109,6 +109,41 @@ class ForceStepper:
         return pos, mom
 
 
+    def step_host(self, hpos: torch.Tensor, hmom: torch.Tensor, out_pos: torch.Tensor, out_mom: torch.Tensor,
+                  dt_kick: float, dt_drift: float, periodic_pp: bool = False):
+        """One kick-drift step on HOST buffers: hpos/hmom/out_pos/out_mom are (Np,3) float64 CPU tensors
+        (pinned for asynchronous copies).  Positions are uploaded first; the momenta — first needed
+        by the kick at the end of the step — are uploaded on a side stream while the force is
+        computed; the updated pos/mom are then copied back.  Asynchronous on the current stream:
+        the caller synchronises before reading out_pos/out_mom."""
+        n = hpos.shape[0]
+        dev = self.eng.device
+        if getattr(self, "_dpos", None) is None or self._dpos.shape[0] != n:
+            self._dpos = torch.empty((n, 3), dtype=torch.float64, device=dev)
+            self._dmom = torch.empty((n, 3), dtype=torch.float64, device=dev)
+            self._side = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        self._side.wait_stream(main)          # the previous step is done with _dmom
+        self._dpos.copy_(hpos, non_blocking=True)
+        with torch.cuda.stream(self._side):
+            self._dmom.copy_(hmom, non_blocking=True)
+        c = self.cfg
+        kick = c.mass * dt_kick
+        drift = dt_drift / (c.mass * c.a * c.a)
+        if c.method == "pm":
+            f, fs = self.pm_mesh(self._dpos)
+            main.wait_stream(self._side)
+            self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, self._dpos, self._dmom, None, 1.0, kick, drift,
+                                       c.boxsize)
+        else:
+            acc = self.accel(self._dpos, periodic_pp)
+            main.wait_stream(self._side)
+            self.eng.kick_drift(self._dpos, self._dmom, acc, kick, drift, c.boxsize)
+        out_pos.copy_(self._dpos, non_blocking=True)
+        out_mom.copy_(self._dmom, non_blocking=True)
+        return out_pos, out_mom
+
+
 def _cfg_from(param):
     if isinstance(param, ForceConfig):
         return param
