@@ -468,7 +468,7 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
                                             i_limit=pos.shape[0])
         t = phase_ms["p3m_short"] * 1e-3
         ach = inr * P3M_FLOP / t / 1e12
-        fp = {"kernel": "p3m_short (K5, warp-per-cell)", "bound": "fp32", "ms": phase_ms["p3m_short"],
+        fp = {"kernel": "p3m_short (K5, v4: 8 i x 4 j-streams, test all / evaluate in-range)", "bound": "fp32", "ms": phase_ms["p3m_short"],
               "achieved": ach, "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
               "flop_per_inrange_pair": P3M_FLOP, "inrange_pairs": inr, "candidate_pairs": cand,
               "candidate_pairs_per_s": cand / t,
