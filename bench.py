@@ -305,6 +305,8 @@ def run_ours(args):
             record.append((name, a, b))
             return r
         if world > 1:
+            if args.subphases and getattr(stepper, "mesh", None) is not None:
+                stepper.mesh.submark = mark
             if method == "pk":
                 return stepper(state["pos"], np_total, mark=mark)
             # migration may hand back new tensors: the particle set of this rank is `state`
@@ -370,6 +372,11 @@ def run_ours(args):
     for name, a, b in recs:
         phases.setdefault(name, []).append(a.elapsed_time(b))
     phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
+    phase_by_rank = None
+    if world > 1:      # every rank's phase times (diagnosis of load imbalance / exposed waits)
+        allp = [None] * world
+        dist.all_gather_object(allp, {k: round(v, 3) for k, v in phase_ms.items()})
+        phase_by_rank = {k: [r.get(k) for r in allp] for k in phase_ms}
     work = float(np_total) ** 2 / 1e9 if method == "pp" else float(np_total)
     value = work / (ms_per_step * 1e-3)
 
@@ -378,6 +385,8 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(wl, n, N, L),
             "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()}, "gpu_launches": int(launches),
             "gpu_launches_note": "kernels of libnbody_b200.so only (cuFFT/cub launches are library code)"}
+    if phase_by_rank is not None:
+        line["phase_ms_by_rank"] = phase_by_rank
     line["config"]["parallelism"] = ("single GPU" if world == 1 else
                                      f"{world} ranks, i-sharded + all-gather of j" if method == "pp" else
                                      f"{world} x-slabs: slab FFT all-to-all, ghost planes, halo particles")
@@ -590,6 +599,7 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="override particles per side (development only)")
     ap.add_argument("--mesh", type=int, default=0, help="override mesh size (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
+    ap.add_argument("--subphases", action="store_true", help="finer CUDA-event marks inside the slab FFT (development only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

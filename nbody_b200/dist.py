@@ -292,16 +292,17 @@ class SlabMesh:
     def forward_all(self, nb: int, first: int = 0):
         """2-D R2C + pack of mesh b+1 overlap the all-to-all of mesh b."""
         lay, eng = self.lay, self.eng
+        sub = getattr(self, "submark", None) or (lambda name, fn: fn())   # optional finer phase timing
         works = []
         for k in range(nb):
             b = first + k
             xb = self.xbufs[k % len(self.xbufs)]
-            eng.slab_fft2d(self.N, lay.nxl, +1, self.rho[b], self.s2d)
-            eng.slab_pack(self.s2d, xb, lay.nxl, lay.world, lay.nyl, lay.nzh)
+            sub("fwd.2d_r2c", lambda: eng.slab_fft2d(self.N, lay.nxl, +1, self.rho[b], self.s2d))
+            sub("fwd.pack", lambda: eng.slab_pack(self.s2d, xb, lay.nxl, lay.world, lay.nyl, lay.nzh))
             works.append(self.comm.all_to_all(self.rhok[b], xb, async_op=True))
         for k in range(nb):
-            works[k].wait()
-            eng.slab_fft1d_x(self.N, lay.rows, +1, self.rhok[first + k])
+            sub("fwd.a2a_wait", lambda: works[k].wait())
+            sub("fwd.1d_x", lambda: eng.slab_fft1d_x(self.N, lay.rows, +1, self.rhok[first + k]))
         return [self.rhok[first + k] for k in range(nb)]
 
     # y-slab spectra g[0:nc] -> real x-slabs force[0:nc] (first nxl planes)
@@ -354,6 +355,7 @@ class DistForceStepper:
         if cfg.method not in ("pp", "pm", "p3m"):
             raise ValueError(f"unknown force method {cfg.method!r}")
         self._acc = None
+        self._pbuf = self._mbuf = None          # capacity buffers: rows [0,n) own particles, then halo / arrivals
         self.mesh = None
         self._mark = lambda name, fn: fn()      # bench.py installs a CUDA-event recorder per step
         if cfg.method in ("pm", "p3m"):
@@ -371,6 +373,26 @@ class DistForceStepper:
         if self._acc is None or self._acc.shape[0] < n:
             self._acc = torch.empty((max(n, 1), 3), dtype=torch.float64, device=self.eng.device)
         return self._acc[:n]
+
+    def _own(self, pos, mom=None):
+        """pos / mom as views (rows [0,n)) of this stepper's capacity buffers.  Halo copies and
+        migrating particles are appended behind row n in place, so a step allocates nothing of
+        the particle set's size (a growing torch.cat per step cost cudaMalloc stalls of 10+ ms
+        on 4 GPUs).  Tensors that are already such views are returned as they are."""
+        n = pos.shape[0]
+        if self._pbuf is None or self._pbuf.shape[0] < n + max(n // 8, 4096):
+            cap = n + max(n // 5, 65536)
+            old_p, old_m = self._pbuf, self._mbuf
+            self._pbuf = torch.empty((cap, 3), dtype=torch.float64, device=self.eng.device)
+            self._mbuf = torch.empty((cap, 3), dtype=torch.float64, device=self.eng.device)
+            del old_p, old_m
+        if pos.data_ptr() != self._pbuf.data_ptr():
+            self._pbuf[:n].copy_(pos)
+            pos = self._pbuf[:n]
+        if mom is not None and mom.data_ptr() != self._mbuf.data_ptr():
+            self._mbuf[:n].copy_(mom)
+            mom = self._mbuf[:n]
+        return pos, mom
 
     # -- long range ---------------------------------------------------------------------------
     def pm_mesh(self, pos):
@@ -417,8 +439,13 @@ class DistForceStepper:
     def short_range(self, pos, acc, accumulate=True):
         c, mk = self.cfg, self._mark
         halo = mk("halo_exchange", lambda: self.halo_exchange(pos))
-        allp = torch.cat([pos, halo]) if halo.shape[0] else pos
-        self.last_halo = int(halo.shape[0])
+        n, h = pos.shape[0], int(halo.shape[0])
+        if h and self._pbuf is not None and pos.data_ptr() == self._pbuf.data_ptr() and n + h <= self._pbuf.shape[0]:
+            self._pbuf[n:n + h].copy_(halo)          # halo copies sit right behind the own particles
+            allp = self._pbuf[:n + h]
+        else:
+            allp = torch.cat([pos, halo]) if h else pos
+        self.last_halo = h
         sorted4, perm, cell_start = mk("cell_sort", lambda: self.eng.cell_sort(allp, c.boxsize, self.ncs, mass=1.0))
         mk("p3m_short", lambda: self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut,
                                                    c.eps, scale=c.G * c.mass, out=acc, accumulate=accumulate,
@@ -466,8 +493,15 @@ class DistForceStepper:
             pos[out_idx[:k]] = arrivals[:k, :3]
             mom[out_idx[:k]] = arrivals[:k, 3:]
         if n_in > n_out:
-            pos = torch.cat([pos, arrivals[k:, :3]])
-            mom = torch.cat([mom, arrivals[k:, 3:]])
+            extra = n_in - n_out
+            if (self._pbuf is not None and pos.data_ptr() == self._pbuf.data_ptr()
+                    and mom.data_ptr() == self._mbuf.data_ptr() and n + extra <= self._pbuf.shape[0]):
+                self._pbuf[n:n + extra].copy_(arrivals[k:, :3])
+                self._mbuf[n:n + extra].copy_(arrivals[k:, 3:])
+                pos, mom = self._pbuf[:n + extra], self._mbuf[:n + extra]
+            else:
+                pos = torch.cat([pos, arrivals[k:, :3]])
+                mom = torch.cat([mom, arrivals[k:, 3:]])
         elif n_out > n_in:
             holes = out_idx[k:]
             n_new = n - holes.shape[0]
@@ -485,6 +519,8 @@ class DistForceStepper:
         acc = self._acc_buf(pos.shape[0])
         if c.method == "pp":
             return self.pp(pos, acc, n_total or c.npart, periodic_pp)
+        if self.world > 1 and c.method == "p3m":
+            pos, _ = self._own(pos)
         self.pm_mesh(pos)
         self._gather(pos, None, acc, 0.0, 0.0)
         if c.method == "p3m":
@@ -503,6 +539,8 @@ class DistForceStepper:
                 self.pp(pos, acc, n_total or c.npart, periodic_pp)
                 mark("kick_drift", lambda: self.eng.kick_drift(pos, mom, acc, kick, drift, c.boxsize))
                 return pos, mom
+            if self.world > 1:
+                pos, mom = self._own(pos, mom)
             self.pm_mesh(pos)
             if c.method == "pm":
                 mark("gather_kick_drift", lambda: self._gather(pos, mom, None, kick, drift))
