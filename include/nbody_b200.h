@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 2
+#define NB_ABI_VERSION 3
 
 #define NB_OK 0
 #define NB_EINVAL (-1)  /* bad argument */
@@ -167,6 +167,14 @@ int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_s
                          double cell, double* pos, double* mom, double* acc_out, int64_t np,
                          double gscale, double kick, double drift, double L, void* stream);
 
+/* As nb_gather_kick_drift(_slab) with g += acc_add[p] (nullable) before acc_out / kick / drift:
+ * the tail of a P3M step whose short-range force was computed concurrently on another stream.
+ * Full mesh: x0 = 0, nx_own = N, n_ghost = 0. */
+int nb_gather_kick_drift_add(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N, int x0,
+                             int nx_own, int n_ghost, double cell, double* pos, double* mom,
+                             const double* acc_add, double* acc_out, int64_t np, double gscale, double kick,
+                             double drift, double L, void* stream);
+
 /* ---- K2  PM / P3M long-range solve --------------------------------------------------------
  * No reference source (CONCEPT-internal; configured by Different_Sizes/Giant.param:28-68,
  * TheFeedingPipeline/NN.param:53-83).  Built from the reference's window
@@ -213,6 +221,10 @@ int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start
                  int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
                  double eps, const double* coef_host, int ncoef, double u_max, double scale,
                  int accumulate, int64_t i_limit, double* acc, void* stream);
+/* Resident CTAs per SM of the nb_p3m_short grid (0 = default: many waves of CTAs).  A value
+ * below the kernel's natural residency (4) leaves shared memory / registers on every SM for
+ * kernels of another stream (the PM chain of the same step runs concurrently). */
+int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm);
 /* Pair statistics of the same traversal: out2[0] = candidate pairs (all j in the 27
  * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]).
  * perm / i_limit as in nb_p3m_short (perm may be NULL when i_limit = 0). */

@@ -38,6 +38,8 @@ PROTOTYPES = {
     "nb_kick_drift": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_f64, c_f64, c_f64, c_vp]),
     "nb_gather_kick_drift": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_f64, c_vp, c_vp, c_vp, c_i64, c_f64, c_f64,
                                      c_f64, c_f64, c_vp]),
+    "nb_gather_kick_drift_add": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp,
+                                         c_i64, c_f64, c_f64, c_f64, c_f64, c_vp]),
     "nb_kspace_fused": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp]),
     "nb_pm_force_mesh": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_vp, c_f64, c_i32, c_i32, c_i32, c_f64,
                                  c_vp, c_vp, c_vp]),
@@ -46,6 +48,7 @@ PROTOTYPES = {
     "nb_cell_sort": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
                              c_f64, c_f64, c_i32, c_i64, c_vp, c_vp]),
+    "nb_p3m_set_ctas_per_sm": (c_i32, [c_vp, c_i32]),
     "nb_p3m_count_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp]),
     "nb_cic_deposit_slab": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_i32, c_i32, c_vp, c_f64, c_i32, c_vp,
                                     c_vp]),
@@ -92,7 +95,7 @@ def load():
     return lib
 
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 def check(rc: int, what: str = ""):

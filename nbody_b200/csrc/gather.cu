@@ -97,8 +97,8 @@ kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const doub
 __global__ void __launch_bounds__(256)
 gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, int x0, int nxp,
                          double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
-                         double* __restrict__ acc_out, int64_t np, double gscale, double kick, double drift,
-                         double L) {
+                         const double* __restrict__ acc_add, double* __restrict__ acc_out, int64_t np,
+                         double gscale, double kick, double drift, double L) {
   const int64_t n3 = (int64_t)nxp * N * N;   // component stride of the field buffers
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
@@ -115,6 +115,9 @@ gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) g[c] *= gscale;
+    if (acc_add) {   // e.g. the P3M short-range part computed concurrently on another stream
+      g[0] += acc_add[3 * p]; g[1] += acc_add[3 * p + 1]; g[2] += acc_add[3 * p + 2];
+    }
     if (acc_out) {
       acc_out[3 * p] = g[0]; acc_out[3 * p + 1] = g[1]; acc_out[3 * p + 2] = g[2];
     }
@@ -173,15 +176,15 @@ extern "C" int nb_kick_drift(nb_ctx* ctx, double* pos, double* mom, const double
 }
 
 static int gkd_launch(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N, int x0, int nxp,
-                      double cell, double* pos, double* mom, double* acc_out, int64_t np, double gscale,
-                      double kick, double drift, double L, cudaStream_t st) {
+                      double cell, double* pos, double* mom, const double* acc_add, double* acc_out, int64_t np,
+                      double gscale, double kick, double drift, double L, cudaStream_t st) {
   NB_REQUIRE(ctx && force3 && (np == 0 || pos), "NULL argument");
   NB_REQUIRE(N >= 1 && cell > 0 && L > 0, "bad N / cell / L");
   NB_REQUIRE(mom || acc_out, "nothing to do: give mom (kick+drift) and/or acc_out");
   if (np == 0) return NB_OK;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   gather_kick_drift_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(
-      force3, force3_shifted, N, x0, nxp, cell, 0.5 * cell, pos, mom, acc_out, np, gscale, kick, drift, L);
+      force3, force3_shifted, N, x0, nxp, cell, 0.5 * cell, pos, mom, acc_add, acc_out, np, gscale, kick, drift, L);
   NB_LAUNCHED(ctx);
   return NB_OK;
 }
@@ -189,8 +192,8 @@ static int gkd_launch(nb_ctx* ctx, const float* force3, const float* force3_shif
 extern "C" int nb_gather_kick_drift(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
                                     double cell, double* pos, double* mom, double* acc_out, int64_t np,
                                     double gscale, double kick, double drift, double L, void* stream) {
-  return gkd_launch(ctx, force3, force3_shifted, N, 0, N, cell, pos, mom, acc_out, np, gscale, kick, drift, L,
-                    (cudaStream_t)stream);
+  return gkd_launch(ctx, force3, force3_shifted, N, 0, N, cell, pos, mom, nullptr, acc_out, np, gscale, kick, drift,
+                    L, (cudaStream_t)stream);
 }
 
 // Slab form: force3 / force3_shifted are [3][nx_own + n_ghost][N][N] and hold the mesh planes
@@ -201,6 +204,17 @@ extern "C" int nb_gather_kick_drift_slab(nb_ctx* ctx, const float* force3, const
                                          double* acc_out, int64_t np, double gscale, double kick, double drift,
                                          double L, void* stream) {
   NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && nx_own <= N && n_ghost >= 0, "bad slab");
-  return gkd_launch(ctx, force3, force3_shifted, N, x0, nx_own + n_ghost, cell, pos, mom, acc_out, np, gscale,
-                    kick, drift, L, (cudaStream_t)stream);
+  return gkd_launch(ctx, force3, force3_shifted, N, x0, nx_own + n_ghost, cell, pos, mom, nullptr, acc_out, np,
+                    gscale, kick, drift, L, (cudaStream_t)stream);
+}
+
+// g = gscale · gather + acc_add[p]: the fused tail of a P3M step whose short-range part was
+// computed concurrently (another stream) into acc_add.  Full mesh: x0 = 0, nx_own = N, n_ghost = 0.
+extern "C" int nb_gather_kick_drift_add(nb_ctx* ctx, const float* force3, const float* force3_shifted, int N,
+                                        int x0, int nx_own, int n_ghost, double cell, double* pos, double* mom,
+                                        const double* acc_add, double* acc_out, int64_t np, double gscale,
+                                        double kick, double drift, double L, void* stream) {
+  NB_REQUIRE(x0 >= 0 && x0 < N && nx_own >= 1 && nx_own <= N && n_ghost >= 0, "bad slab");
+  return gkd_launch(ctx, force3, force3_shifted, N, x0, nx_own + n_ghost, cell, pos, mom, acc_add, acc_out, np,
+                    gscale, kick, drift, L, (cudaStream_t)stream);
 }

@@ -809,6 +809,12 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
+  NB_REQUIRE(ctx && ctas_per_sm >= 0 && ctas_per_sm <= 64, "ctas_per_sm must be in [0, 64]");
+  ctx->p3m_ctas_per_sm = ctas_per_sm;
+  return NB_OK;
+}
+
 // coef_host: P3M_DEG+1 doubles (monomial coefficients of Q in t, low to high), HOST pointer.
 extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
                             int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
@@ -833,7 +839,7 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   for (int d = 0; d <= P3M_DEG; ++d) prm.coef[d] = (float)coef_host[d];
   const int ilim = (i_limit <= 0 || i_limit > 0x7fffffff) ? 0x7fffffff : (int)i_limit;
   const int64_t ncell = cell_hi - cell_lo;
-  const int64_t cap = (int64_t)ctx->num_sms * 64;
+  const int64_t cap = (int64_t)ctx->num_sms * (ctx->p3m_ctas_per_sm > 0 ? ctx->p3m_ctas_per_sm : 64);
   // v4 (two-phase: test all, evaluate in-range only) is the default; NB_P3M_KERNEL selects the
   // older kernels for A/B measurements: 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
   // compaction, 3 = v3 packed evaluate-all, 5 = v3's loop on v4's flattened tile fill.

@@ -541,14 +541,17 @@ class DistForceStepper:
                 return pos, mom
             if self.world > 1:
                 pos, mom = self._own(pos, mom)
-            self.pm_mesh(pos)
             if c.method == "pm":
+                self.pm_mesh(pos)
                 mark("gather_kick_drift", lambda: self._gather(pos, mom, None, kick, drift))
-            else:
-                acc = self._acc_buf(pos.shape[0])
-                mark("gather", lambda: self._gather(pos, None, acc, 0.0, 0.0))
-                self.short_range(pos, acc, True)
-                mark("kick_drift", lambda: self.eng.kick_drift(pos, mom, acc, kick, drift, c.boxsize))
+            else:   # short range into its own buffer, mesh chain, one fused gather + add + kick + drift
+                acc_s = self._acc_buf(pos.shape[0])
+                self.short_range(pos, acc_s, False)
+                f, fs = self.pm_mesh(pos)
+                lay = self.mesh.lay
+                mark("gather_kick_drift", lambda: self.eng.gather_kick_drift_add(
+                    f, fs, c.gridsize, c.cell, pos, mom, acc_s, None, 1.0, kick, drift, c.boxsize, x0=lay.x0,
+                    nx_own=lay.nxl, n_ghost=lay.n_ghost))
             return mark("migrate", lambda: self.migrate(pos, mom))
         finally:
             self._mark = lambda name, fn: fn()

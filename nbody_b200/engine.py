@@ -237,6 +237,18 @@ class Engine:
                    "nb_gather_kick_drift")
 
     # -- K2 ---------------------------------------------------------------------------
+    def gather_kick_drift_add(self, force3, force3_shifted, N, cell, pos, mom, acc_add, acc_out, gscale, kick, drift,
+                              L, x0=0, nx_own=None, n_ghost=0):
+        """g = gscale·gather + acc_add; acc_out (nullable) <- g; kick/drift if mom is given."""
+        self._check_pos(pos)
+        _lib.check(self.lib.nb_gather_kick_drift_add(
+            self.ctx, _ptr(force3), _ptr(force3_shifted), int(N), int(x0), int(N if nx_own is None else nx_own),
+            int(n_ghost), float(cell), _ptr(pos), _ptr(mom), _ptr(acc_add), _ptr(acc_out), pos.shape[0],
+            float(gscale), float(kick), float(drift), float(L), self.stream), "nb_gather_kick_drift_add")
+
+    def p3m_set_ctas_per_sm(self, n: int):
+        _lib.check(self.lib.nb_p3m_set_ctas_per_sm(self.ctx, int(n)), "nb_p3m_set_ctas_per_sm")
+
     def pm_force_mesh(self, pos: torch.Tensor, L: float, N: int, r_s: float = 0.0, deconv_order: int = 2,
                       interlace_up: bool = False, interlace_down: bool = False, pref: float = 1.0,
                       out: torch.Tensor | None = None, out_shifted: torch.Tensor | None = None):

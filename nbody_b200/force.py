@@ -12,6 +12,7 @@ a kernel of libnbody_b200.so (via engine.Engine); there is no CPU path.
 from __future__ import annotations
 
 import math
+import os
 
 import numpy as np
 import torch
@@ -39,6 +40,17 @@ class ForceStepper:
             self.ncs = int(math.floor(cfg.boxsize / cfg.r_cut))
             if self.ncs < 3:
                 raise ValueError("P3M short range needs boxsize >= 3 r_cut")
+        # P3M: the short-range part goes into its own buffer and ONE fused tail kernel does
+        # gather(mesh) + short -> kick -> drift.  NB_P3M_OVERLAP=1 additionally runs the mesh chain
+        # and the pair kernel concurrently on two streams (pair-kernel grid held to NB_P3M_CTAS
+        # CTAs per SM).  Measured on B200 at config 5: 185-231 ms against 184 ms
+        # one after the other — the pair kernel is latency-bound and needs all of an SM's shared
+        # memory, cuFFT's 64 KB CTAs do not fit beside it — so the default is sequential.
+        self.fused_tail = cfg.method == "p3m"
+        self.overlap = cfg.method == "p3m" and os.environ.get("NB_P3M_OVERLAP", "0") == "1"
+        self.p3m_ctas = int(os.environ.get("NB_P3M_CTAS", "4"))
+        self._acc_s = None
+        self._streams = None
 
     # -- buffers --------------------------------------------------------------------------
     def _acc_buf(self, n):
@@ -81,6 +93,40 @@ class ForceStepper:
                           variant=self.pp_variant, out=acc)
         return acc
 
+    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None):
+        """Cell sort + pair kernel into a separate buffer, mesh chain, then ONE fused kernel:
+        g = gather(mesh) + short; acc_out <- g and/or kick + drift.  With self.overlap the two
+        parts run on two streams (mesh chain on a high-priority one)."""
+        c, eng = self.cfg, self.eng
+        dev = eng.device
+        n = pos.shape[0]
+        if self._acc_s is None or self._acc_s.shape[0] != n:
+            self._acc_s = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        main = torch.cuda.current_stream(dev)
+        if self.overlap:
+            if self._streams is None:
+                self._streams = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
+            pm_stream, sr_stream = self._streams
+            pm_stream.wait_stream(main)
+            sr_stream.wait_stream(main)
+            eng.p3m_set_ctas_per_sm(self.p3m_ctas)
+            try:
+                with torch.cuda.stream(sr_stream):
+                    self.short_range(pos, self._acc_s, accumulate=False)
+                with torch.cuda.stream(pm_stream):
+                    f, fs = self.pm_mesh(pos)
+            finally:
+                eng.p3m_set_ctas_per_sm(0)
+            main.wait_stream(pm_stream)
+            main.wait_stream(sr_stream)
+        else:
+            self.short_range(pos, self._acc_s, accumulate=False)
+            f, fs = self.pm_mesh(pos)
+        if tail_waits is not None:            # e.g. the momentum upload of step_host
+            main.wait_stream(tail_waits)
+        eng.gather_kick_drift_add(f, fs, c.gridsize, c.cell, pos, mom, self._acc_s, acc_out, 1.0, kick, drift,
+                                  c.boxsize)
+
     # -- public ---------------------------------------------------------------------------
     def accel(self, pos: torch.Tensor, periodic_pp: bool = False) -> torch.Tensor:
         """Acceleration at the particles, (Np,3) float64 (no kick/drift)."""
@@ -88,6 +134,9 @@ class ForceStepper:
         acc = self._acc_buf(pos.shape[0])
         if c.method == "pp":
             return self.pp(pos, acc, periodic_pp)
+        if self.fused_tail:
+            self._p3m_fused(pos, None, acc, 0.0, 0.0)
+            return acc
         f, fs = self.pm_mesh(pos)
         self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, pos, None, acc, 1.0, 0.0, 0.0, c.boxsize)
         if c.method == "p3m":
@@ -103,6 +152,9 @@ class ForceStepper:
         if c.method == "pm":
             f, fs = self.pm_mesh(pos)
             self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, pos, mom, None, 1.0, kick, drift, c.boxsize)
+            return pos, mom
+        if self.fused_tail:
+            self._p3m_fused(pos, mom, None, kick, drift)
             return pos, mom
         acc = self.accel(pos, periodic_pp)
         self.eng.kick_drift(pos, mom, acc, kick, drift, c.boxsize)
@@ -135,6 +187,8 @@ class ForceStepper:
             main.wait_stream(self._side)
             self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, self._dpos, self._dmom, None, 1.0, kick, drift,
                                        c.boxsize)
+        elif self.fused_tail:
+            self._p3m_fused(self._dpos, self._dmom, None, kick, drift, tail_waits=self._side)
         else:
             acc = self.accel(self._dpos, periodic_pp)
             main.wait_stream(self._side)
