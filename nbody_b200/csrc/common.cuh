@@ -2,7 +2,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cufft.h>
+#include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <stdio.h>
 #include <string.h>
 #include <map>
@@ -110,6 +112,33 @@ int nb_plan_many(nb_ctx* ctx, int rank, const int* n, int batch, cufftType type,
 int nb_exec_c2r(nb_ctx* ctx, cufftHandle plan, int prec, void* spec, void* dst, size_t real_bytes,
                 cudaStream_t st);
 
+// Traversal order of the particle kernels (deposit, gather).  Snapshots and the Zel'dovich /
+// glass initial conditions are in lattice order (ix, iy, iz; iz fastest), so the particles that
+// share mesh sectors with particle p sit 1, n and n² entries away; the n² neighbours are ~100 MB
+// of mesh footprint apart in a linear sweep and their shared sectors fall out of L2 in between.
+// When Np = n³ the kernels therefore sweep y-blocks of NB_YBLOCK lattice rows (for each block:
+// all ix, rows of the block, all iz), which brings the x-neighbours within n·NB_YBLOCK entries.
+// It is only a processing ORDER: every particle is still visited exactly once and inputs that
+// are not lattice ordered are neither helped nor harmed.  Returns the block height (0 = linear).
+// NB_LINEAR_ORDER=1 switches the blocked sweep off, NB_YBLOCK=<rows> overrides its height (A/B runs)
+static inline bool nb_blocked_enabled() {
+  static const bool on = [] { const char* e = getenv("NB_LINEAR_ORDER"); return !(e && atoi(e) == 1); }();
+  return on;
+}
+static inline int nb_lattice_yblock(int64_t np, int* n_out) {
+  *n_out = 0;
+  if (np < 16 * 16 * 16 || np >= ((int64_t)1 << 31)) return 0;
+  int64_t n = (int64_t)(cbrt((double)np) + 0.5);
+  if (n * n * n != np) return 0;
+  *n_out = (int)n;
+  static const int forced = [] { const char* e = getenv("NB_YBLOCK"); return e ? atoi(e) : 0; }();
+  if (forced > 0 && n % forced == 0) return forced;
+  if (n % 32 == 0 && n >= 64) return 32;
+  if (n % 16 == 0 && n >= 32) return 16;
+  if (n % 8 == 0) return 8;      // small sets: no benefit, but keeps the path under the parity tests
+  return 0;
+}
+
 static inline int nb_grid_for(const nb_ctx* ctx, int64_t work_items, int block, int max_waves = 8) {
   int64_t want = (work_items + block - 1) / block;
   int64_t cap = (int64_t)ctx->num_sms * max_waves;
@@ -121,6 +150,17 @@ static inline int nb_grid_for(const nb_ctx* ctx, int64_t work_items, int block, 
 // device helpers: float64 index math that must match numpy/numba bit for bit
 // ---------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+// q-th particle of the y-blocked sweep (see nb_lattice_yblock); yb = 0 -> linear order
+__device__ __forceinline__ int64_t nb_blocked_order(int64_t q, int n, int yb) {
+  if (yb == 0) return q;
+  const unsigned per_x = (unsigned)(yb * n), per_block = per_x * (unsigned)n;
+  const unsigned uq = (unsigned)q;
+  const unsigned b = uq / per_block, r = uq - b * per_block;
+  const unsigned ix = r / per_x, r2 = r - ix * per_x;
+  const unsigned iyl = r2 / (unsigned)n, iz = r2 - iyl * (unsigned)n;
+  return ((int64_t)ix * n + (b * (unsigned)yb + iyl)) * n + iz;
+}
+
 // Python/numpy float modulo: result carries the sign of the divisor.
 __device__ __forceinline__ double nb_pymod(double a, double b) {
   double r = fmod(a, b);
@@ -147,6 +187,48 @@ __device__ __forceinline__ double nb_cell_frac(double p, double cell) {
 }
 
 __device__ __forceinline__ int nb_wrap1(int i, int N) { return i + 1 == N ? 0 : i + 1; }
+
+// Cell index and in-cell fraction of one coordinate.
+//   EXACT = true : idx = int(p/cell) % N and frac = (p % cell)/cell exactly as numpy evaluates
+//                  them (two IEEE divisions and an fmod per coordinate; float64-grid API).
+//   EXACT = false: the SAME idx, bit for bit, without the divisions: q~ = p * (1/cell) is within
+//                  1.5 * 2^-52 * Q of both the exact quotient Q and the rounded one RN(Q) that
+//                  numpy truncates; for 0 <= Q < 2^20 that is < 3.5e-10, so whenever q~ is
+//                  further than 2^-29 from an integer, trunc(q~) == trunc(RN(Q)) == floor(Q).
+//                  Anything else (negative p, huge p, q~ near an integer) takes the exact path.
+//                  p % cell = p - floor(Q) * cell is exactly representable, so one FMA returns
+//                  it exactly; frac = (p % cell) * (1/cell) is within 1 ulp of the reference's
+//                  division (weights carry a 1e-5 tolerance, indices none).
+template <bool EXACT>
+__device__ __forceinline__ void nb_cell_split(double p, double cell, double inv_cell, int N, int& idx,
+                                              double& frac) {
+  if constexpr (!EXACT) {
+    const double MAGIC = 6755399441055744.0;   // 1.5 * 2^52: (q + MAGIC) - MAGIC = rint(q)
+    const double qt = __dmul_rn(p, inv_cell);
+    const double a = __dadd_rn(qt, MAGIC);
+    const double r = __dsub_rn(a, MAGIC);
+    const double f = __dsub_rn(qt, r);         // exact, in [-0.5, 0.5]
+    if (p >= 0.0 && qt < 1048576.0 && fabs(f) > 1.862645149230957e-09) {
+      const bool below = f < 0.0;
+      const int t = __double2loint(a) - (below ? 1 : 0);   // low word of q + MAGIC = rint(q)
+      const double td = below ? __dsub_rn(r, 1.0) : r;
+      frac = __dmul_rn(__fma_rn(-td, cell, p), inv_cell);
+      idx = t >= N ? t % N : t;
+      return;
+    }
+  }
+  idx = nb_cell_index(p, cell, N);
+  frac = nb_cell_frac(p, cell);
+}
+
+// pymod(v, L) for L > 0 without fmod when v is within one box length of [0, L): v - L is exact
+// for L <= v < 2L (Sterbenz), and for -L <= v < 0 Python returns RN(fmod(v, L) + L) = RN(v + L).
+__device__ __forceinline__ double nb_pymod_near(double v, double L) {
+  if (v >= 0.0 && v < L) return v;
+  if (v >= L && v < __dadd_rn(L, L)) return __dsub_rn(v, L);
+  if (v < 0.0 && v >= -L) return __dadd_rn(v, L);
+  return nb_pymod(v, L);
+}
 
 __device__ __forceinline__ float nb_warp_sum(float v) {
 #pragma unroll

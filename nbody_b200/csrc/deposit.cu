@@ -33,21 +33,25 @@ template <typename T, bool VEC2>
 __global__ void __launch_bounds__(256)
 cic_deposit_direct(const double* __restrict__ pos, int64_t np, double cell, int N, int x0, int nxp,
                    T* __restrict__ grid, double shift, int32_t* __restrict__ dbg,
-                   unsigned long long* __restrict__ n_outside) {
+                   unsigned long long* __restrict__ n_outside, int lat_n, int lat_yb) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+  const double inv_cell = __ddiv_rn(1.0, cell);
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < np; q += stride) {
+    const int64_t p = nb_blocked_order(q, lat_n, lat_yb);
     double x = pos[3 * p + 0], y = pos[3 * p + 1], z = pos[3 * p + 2];
     if (shift != 0.0) {
       x = __dadd_rn(x, shift);
       y = __dadd_rn(y, shift);
       z = __dadd_rn(z, shift);
     }
-    const int i0 = nb_cell_index(x, cell, N);
-    const int j0 = nb_cell_index(y, cell, N);
-    const int k0 = nb_cell_index(z, cell, N);
-    const double dx = nb_cell_frac(x, cell);
-    const double dy = nb_cell_frac(y, cell);
-    const double dz = nb_cell_frac(z, cell);
+    // float64 grids keep numpy's divisions; float32 grids use the division-free form (same
+    // indices bit for bit, weights within 1 ulp of float64 — see nb_cell_split)
+    constexpr bool EXACT = sizeof(T) == 8;
+    int i0, j0, k0;
+    double dx, dy, dz;
+    nb_cell_split<EXACT>(x, cell, inv_cell, N, i0, dx);
+    nb_cell_split<EXACT>(y, cell, inv_cell, N, j0, dy);
+    nb_cell_split<EXACT>(z, cell, inv_cell, N, k0, dz);
     if (dbg) {
       dbg[3 * p + 0] = i0;
       dbg[3 * p + 1] = j0;
@@ -96,16 +100,18 @@ static int deposit_launch(nb_ctx* ctx, const double* pos, int64_t np, double cel
   if (np == 0) return NB_OK;
   const int block = 256;
   const int nblk = nb_grid_for(ctx, np, block, 16);
+  int lat_n = 0;
+  const int lat_yb = nb_blocked_enabled() ? nb_lattice_yblock(np, &lat_n) : 0;
   static const int scalar_red = [] { const char* e = getenv("NB_DEPOSIT_SCALAR"); return e && atoi(e) == 1; }();
   if (prec == NB_F64)
     cic_deposit_direct<double, false><<<nblk, block, 0, st>>>(pos, np, cell, N, x0, nxp, (double*)grid, shift,
-                                                              dbg_index, n_outside);
+                                                              dbg_index, n_outside, lat_n, lat_yb);
   else if (scalar_red || (N & 1))   // odd N: rows are not 8-byte aligned
     cic_deposit_direct<float, false><<<nblk, block, 0, st>>>(pos, np, cell, N, x0, nxp, (float*)grid, shift,
-                                                             dbg_index, n_outside);
+                                                             dbg_index, n_outside, lat_n, lat_yb);
   else
     cic_deposit_direct<float, true><<<nblk, block, 0, st>>>(pos, np, cell, N, x0, nxp, (float*)grid, shift,
-                                                            dbg_index, n_outside);
+                                                            dbg_index, n_outside, lat_n, lat_yb);
   NB_LAUNCHED(ctx);
   return NB_OK;
 }

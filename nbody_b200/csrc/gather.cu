@@ -15,12 +15,15 @@ struct CicStencil {
 // mesh has x0 = 0, nxp = N, a slab has nxp = own + ghost planes.  A stencil that does not fit
 // the buffer (a particle this slab does not own) gets zero weights on plane 0: no out-of-range
 // access, contributes nothing.
-__device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, double cell, int N, int x0 = 0,
-                                                  int nxp = 0x7fffffff) {
+template <bool EXACT>
+__device__ __forceinline__ CicStencil cic_stencil(double x, double y, double z, double cell, double inv_cell, int N,
+                                                  int x0 = 0, int nxp = 0x7fffffff) {
   CicStencil s;
-  const int i0 = nb_cell_index(x, cell, N), j0 = nb_cell_index(y, cell, N);
-  s.k0 = nb_cell_index(z, cell, N);
-  const double dx = nb_cell_frac(x, cell), dy = nb_cell_frac(y, cell), dz = nb_cell_frac(z, cell);
+  int i0, j0;
+  double dx, dy, dz;
+  nb_cell_split<EXACT>(x, cell, inv_cell, N, i0, dx);
+  nb_cell_split<EXACT>(y, cell, inv_cell, N, j0, dy);
+  nb_cell_split<EXACT>(z, cell, inv_cell, N, s.k0, dz);
   const int j1 = nb_wrap1(j0, N);
   s.k1 = nb_wrap1(s.k0, N);
   int pa = i0 - x0, pb = nb_wrap1(i0, N) - x0;
@@ -58,13 +61,16 @@ __device__ __forceinline__ double cic_interp(const T* __restrict__ f, const CicS
 template <typename T>
 __global__ void __launch_bounds__(256)
 cic_gather_kernel(const T* __restrict__ field, int ncomp, int N, const double* __restrict__ pos, int64_t np,
-                  double cell, double shift, double* __restrict__ out, int accumulate, double scale) {
+                  double cell, double shift, double* __restrict__ out, int accumulate, double scale, int lat_n,
+                  int lat_yb) {
   const int64_t n3 = (int64_t)N * N * N;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+  const double inv_cell = __ddiv_rn(1.0, cell);
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < np; q += stride) {
+    const int64_t p = nb_blocked_order(q, lat_n, lat_yb);
     double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
     if (shift != 0.0) { x = __dadd_rn(x, shift); y = __dadd_rn(y, shift); z = __dadd_rn(z, shift); }
-    const CicStencil s = cic_stencil(x, y, z, cell, N);
+    const CicStencil s = cic_stencil<sizeof(T) == 8>(x, y, z, cell, inv_cell, N);
     for (int c = 0; c < ncomp; ++c) {
       const double v = cic_interp(field + c * n3, s) * scale;
       if (accumulate) out[p * ncomp + c] += v; else out[p * ncomp + c] = v;
@@ -77,7 +83,7 @@ __global__ void __launch_bounds__(256)
 displace_wrap_kernel(double* __restrict__ pos, const double* __restrict__ disp, int64_t n3, double L) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride)
-    pos[t] = nb_pymod(__dadd_rn(pos[t], disp[t]), L);
+    pos[t] = nb_pymod_near(__dadd_rn(pos[t], disp[t]), L);
 }
 
 // mom += kick * acc ; pos = pymod(pos + drift * mom, L)
@@ -88,7 +94,7 @@ kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const doub
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride) {
     const double m = mom[t] + kick * acc[t];
     mom[t] = m;
-    pos[t] = nb_pymod(pos[t] + drift * m, L);
+    pos[t] = nb_pymod_near(pos[t] + drift * m, L);
   }
 }
 
@@ -98,18 +104,20 @@ __global__ void __launch_bounds__(256)
 gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, int x0, int nxp,
                          double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
                          const double* __restrict__ acc_add, double* __restrict__ acc_out, int64_t np,
-                         double gscale, double kick, double drift, double L) {
+                         double gscale, double kick, double drift, double L, int lat_n, int lat_yb) {
   const int64_t n3 = (int64_t)nxp * N * N;   // component stride of the field buffers
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+  const double inv_cell = __ddiv_rn(1.0, cell);
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < np; q += stride) {
+    const int64_t p = nb_blocked_order(q, lat_n, lat_yb);
     const double x = pos[3 * p], y = pos[3 * p + 1], z = pos[3 * p + 2];
-    const CicStencil s = cic_stencil(x, y, z, cell, N, x0, nxp);
+    const CicStencil s = cic_stencil<false>(x, y, z, cell, inv_cell, N, x0, nxp);
     double g[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) g[c] = cic_interp(f1 + c * n3, s);
     if (f2) {
-      const CicStencil s2 =
-          cic_stencil(__dadd_rn(x, shift2), __dadd_rn(y, shift2), __dadd_rn(z, shift2), cell, N, x0, nxp);
+      const CicStencil s2 = cic_stencil<false>(__dadd_rn(x, shift2), __dadd_rn(y, shift2), __dadd_rn(z, shift2),
+                                               cell, inv_cell, N, x0, nxp);
 #pragma unroll
       for (int c = 0; c < 3; ++c) g[c] = 0.5 * (g[c] + cic_interp(f2 + c * n3, s2));
     }
@@ -127,7 +135,7 @@ gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__
       for (int c = 0; c < 3; ++c) {
         const double m = mom[3 * p + c] + kick * g[c];
         mom[3 * p + c] = m;
-        pos[3 * p + c] = nb_pymod(px[c] + drift * m, L);
+        pos[3 * p + c] = nb_pymod_near(px[c] + drift * m, L);
       }
     }
   }
@@ -144,10 +152,14 @@ extern "C" int nb_cic_gather(nb_ctx* ctx, const void* field, int ncomp, int N, i
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   const int nblk = nb_grid_for(ctx, np, 256, 16);
+  int lat_n = 0;
+  const int lat_yb = nb_blocked_enabled() ? nb_lattice_yblock(np, &lat_n) : 0;
   if (prec == NB_F64)
-    cic_gather_kernel<double><<<nblk, 256, 0, st>>>((const double*)field, ncomp, N, pos, np, cell, shift, out, accumulate, scale);
+    cic_gather_kernel<double><<<nblk, 256, 0, st>>>((const double*)field, ncomp, N, pos, np, cell, shift, out,
+                                                    accumulate, scale, lat_n, lat_yb);
   else
-    cic_gather_kernel<float><<<nblk, 256, 0, st>>>((const float*)field, ncomp, N, pos, np, cell, shift, out, accumulate, scale);
+    cic_gather_kernel<float><<<nblk, 256, 0, st>>>((const float*)field, ncomp, N, pos, np, cell, shift, out,
+                                                   accumulate, scale, lat_n, lat_yb);
   NB_LAUNCHED(ctx);
   return NB_OK;
 }
@@ -183,8 +195,11 @@ static int gkd_launch(nb_ctx* ctx, const float* force3, const float* force3_shif
   NB_REQUIRE(mom || acc_out, "nothing to do: give mom (kick+drift) and/or acc_out");
   if (np == 0) return NB_OK;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  int lat_n = 0;
+  const int lat_yb = nb_blocked_enabled() ? nb_lattice_yblock(np, &lat_n) : 0;
   gather_kick_drift_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(
-      force3, force3_shifted, N, x0, nxp, cell, 0.5 * cell, pos, mom, acc_add, acc_out, np, gscale, kick, drift, L);
+      force3, force3_shifted, N, x0, nxp, cell, 0.5 * cell, pos, mom, acc_add, acc_out, np, gscale, kick, drift, L,
+      lat_n, lat_yb);
   NB_LAUNCHED(ctx);
   return NB_OK;
 }

@@ -2,15 +2,29 @@
 #include "common.cuh"
 
 // ------------------------------------------------------------------ sum of a grid (float64)
+// 16-byte loads, four independent float64 partial sums per thread (the grid is streamed once).
 template <typename T>
 __global__ void __launch_bounds__(256) grid_sum_kernel(const T* __restrict__ g, int64_t n, double* out) {
-  double acc = 0.0;
+  constexpr int V = 16 / sizeof(T);                 // elements per 16-byte vector
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) acc += (double)g[i];
-  acc = nb_warp_sum(acc);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t nvec = 0;
+  if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+    nvec = n / V;
+    const int4* gv = reinterpret_cast<const int4*>(g);
+    for (int64_t i = tid; i < nvec; i += stride) {
+      const int4 raw = __ldg(gv + i);
+      const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k & 3] += (double)e[k];
+    }
+  }
+  for (int64_t i = nvec * V + tid; i < n; i += stride) acc[0] += (double)g[i];
+  double a = nb_warp_sum((acc[0] + acc[1]) + (acc[2] + acc[3]));
   __shared__ double part[8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (lane == 0) part[w] = acc;
+  if (lane == 0) part[w] = a;
   __syncthreads();
   if (w == 0) {
     double v = lane < (blockDim.x >> 5) ? part[lane] : 0.0;
@@ -25,7 +39,7 @@ extern "C" int nb_grid_sum(nb_ctx* ctx, const void* grid, int64_t n, int prec, d
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   NB_CHECK_CUDA(cudaMemsetAsync(out_sum, 0, sizeof(double), st));
-  const int nblk = nb_grid_for(ctx, n / 4 + 1, 256, 4);
+  const int nblk = nb_grid_for(ctx, n / 4 + 1, 256, 8);
   if (prec == NB_F64)
     grid_sum_kernel<double><<<nblk, 256, 0, st>>>((const double*)grid, n, out_sum);
   else
@@ -35,18 +49,45 @@ extern "C" int nb_grid_sum(nb_ctx* ctx, const void* grid, int64_t n, int prec, d
 }
 
 // ------------------------------------------------------------------ grid <- (grid/a)/b - c
+// float64 grids keep the reference's two IEEE divisions (compute_delta, FraP_kTilDelta.py:126;
+// Power_compare.py:153-159).  float32 grids multiply by the float64 reciprocals instead: the
+// float64 result differs by <= 2 ulp(double) before it is rounded to float32, far inside the
+// 1e-5 tolerance of the float32 path, and the kernel becomes a 16-byte-vector stream.
+template <typename T>
+__device__ __forceinline__ T grid_affine_one(T x, double a, double b, double ra, double rb, double c) {
+  double v = (double)x;
+  if constexpr (sizeof(T) == 8) {
+    if (a != 1.0) v = __ddiv_rn(v, a);
+    if (b != 1.0) v = __ddiv_rn(v, b);
+  } else {
+    if (a != 1.0) v = __dmul_rn(v, ra);
+    if (b != 1.0) v = __dmul_rn(v, rb);
+  }
+  return (T)__dsub_rn(v, c);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 grid_affine_kernel(T* __restrict__ g, int64_t n, double a, const double* __restrict__ a_dev, double a_div,
                    double b, double c) {
   if (a_dev) a = __ddiv_rn(*a_dev, a_div);
+  const double ra = __ddiv_rn(1.0, a), rb = __ddiv_rn(1.0, b);
+  constexpr int V = 16 / sizeof(T);
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    double v = (double)g[i];
-    if (a != 1.0) v = __ddiv_rn(v, a);
-    if (b != 1.0) v = __ddiv_rn(v, b);
-    g[i] = (T)__dsub_rn(v, c);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t nvec = 0;
+  if ((reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+    nvec = n / V;
+    int4* gv = reinterpret_cast<int4*>(g);
+    for (int64_t i = tid; i < nvec; i += stride) {
+      int4 raw = gv[i];
+      T* e = reinterpret_cast<T*>(&raw);
+#pragma unroll
+      for (int k = 0; k < V; ++k) e[k] = grid_affine_one<T>(e[k], a, b, ra, rb, c);
+      gv[i] = raw;
+    }
   }
+  for (int64_t i = nvec * V + tid; i < n; i += stride) g[i] = grid_affine_one<T>(g[i], a, b, ra, rb, c);
 }
 
 extern "C" int nb_grid_affine(nb_ctx* ctx, void* grid, int64_t n, int prec, double a, const double* a_dev,
@@ -55,7 +96,7 @@ extern "C" int nb_grid_affine(nb_ctx* ctx, void* grid, int64_t n, int prec, doub
   NB_REQUIRE(prec == NB_F32 || prec == NB_F64, "bad prec");
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
-  const int nblk = nb_grid_for(ctx, n, 256, 8);
+  const int nblk = nb_grid_for(ctx, n / 4 + 1, 256, 8);
   if (prec == NB_F64)
     grid_affine_kernel<double><<<nblk, 256, 0, st>>>((double*)grid, n, a, a_dev, a_div, b, c);
   else

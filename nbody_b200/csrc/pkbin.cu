@@ -15,6 +15,8 @@
 // equal bins form contiguous lane segments; a segmented shuffle reduction leaves one
 // (count,sum) per segment, written by the segment head into a warp-private shared-memory
 // histogram (no atomics).  CTAs flush their histograms to global memory once at the end.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #define PK_WARPS 8
@@ -133,8 +135,287 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const do
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// pk_shell_bin_rows_kernel — the complex64 production path (HBM-bound form).
+//
+// The kernel above spends ~100 warp instructions per 32 modes on the bin search and the
+// segmented shuffle reduction and keeps one 256-byte load in flight per warp.  This one turns
+// the mapping by 90 degrees: a LANE owns one (kx,ky) row and walks it along kz, so the
+// monotone bin index becomes a running register (g, next two thresholds) and a partial sum
+// stays in registers until the row crosses a shell boundary (about every 27 modes at the C5
+// size).  The 32 rows of a warp are contiguous in memory; 16-mode pieces of them are staged
+// through shared memory with 8-byte cp.async in a 2- or 3-deep pipeline (coalesced 128-byte row
+// segments in, conflict-free LDS.128 per lane out; row pitch 144 B), which keeps
+// ~8 KB per warp in flight.
+//   * kz = 1 .. N/2-1 (weight 2) is the streamed range; the two weight-1 columns kz = 0 and
+//     kz = N/2 are binned by a generic search at the start of each row;
+//   * a 16-mode piece with at most one shell boundary is summed branch-free into a "current"
+//     and a "next" float accumulator (x < th1 selects); pieces with more boundaries (low |k|
+//     only) take a per-mode loop;
+//   * partial sums are flushed into ONE shared histogram per CTA (native u32 atomics for the
+//     counts, CAS-loop f64 adds for the sums — a flush happens once per ~27 modes), which goes
+//     to global memory once, scaled by `norm`, at the end.
+// Bin decisions use the same float64 k² tables and thresholds as above: counts stay bit-exact.
+#define PKF_WARPS 4
+#define PKF_CHUNK 16
+#define PKF_PITCH (PKF_CHUNK * 8 + 16)          // bytes per staged row piece
+#define PKF_STAGE_BYTES (32 * PKF_PITCH)
+
+__device__ __forceinline__ int pkf_find_bin(double x, const double* __restrict__ s_th, int n_edges,
+                                            float log2_k2min, float inv_dlog2) {
+  int g = (int)floorf((__log2f((float)x) - log2_k2min) * inv_dlog2);
+  g = max(-1, min(g, n_edges - 1));
+  while (g + 1 < n_edges && s_th[g + 1] <= x) ++g;
+  while (g >= 0 && s_th[g] > x) --g;
+  return g;   // (#thresholds <= x) - 1
+}
+
+__device__ __forceinline__ void pkf_flush(double* s_sums, unsigned* s_cnt, int nb, int g, double acc,
+                                          unsigned cnt, unsigned wt) {
+  if (g >= 0 && g < nb && cnt) {
+    atomicAdd(&s_cnt[g], cnt * wt);
+    atomicAdd(&s_sums[g], acc * (double)wt);
+  }
+}
+
+// Warp-collective flush (all 32 lanes call it, converged).  The 32 rows of a warp are
+// neighbours in k-space, so lanes that cross a shell boundary in the same piece mostly flush
+// into the SAME bin; sent one by one they serialise in the CAS loop of the shared f64 add.
+// Lanes are grouped by bin (leader loop), each group is summed with shuffles and its leader
+// issues one add.
+__device__ __forceinline__ void pkf_flush_warp(double* s_sums, unsigned* s_cnt, int nb, bool want, int g,
+                                               double acc, unsigned cnt, unsigned wt, int lane) {
+  bool pend = want && g >= 0 && g < nb && cnt != 0;
+  unsigned m = __ballot_sync(0xffffffffu, pend);
+  while (m) {
+    const int leader = __ffs(m) - 1;
+    const int gl = __shfl_sync(0xffffffffu, g, leader);
+    const bool mine = pend && g == gl;
+    const unsigned mm = __ballot_sync(0xffffffffu, mine);
+    double a = mine ? acc : 0.0;
+    unsigned c = mine ? cnt : 0u;
+    if (mm & (mm - 1)) {   // more than one lane in this group
+      a = nb_warp_sum(a);
+      c = __reduce_add_sync(0xffffffffu, c);
+    }
+    if (lane == leader) {
+      atomicAdd(&s_cnt[gl], c * wt);
+      atomicAdd(&s_sums[gl], a * (double)wt);
+    }
+    m &= ~mm;
+    pend = pend && !mine;
+  }
+}
+
+template <bool WINDOW>
+__device__ __forceinline__ float pkf_power(float2 v, double sxy, double sz, int window_power, int clip_mode,
+                                           double clip_val) {
+  float p = v.x * v.x + v.y * v.y;
+  if constexpr (WINDOW) {
+    double w = __dmul_rn(sxy, sz);
+    w = __dmul_rn(w, w);
+    if (clip_mode == 1) {
+      if (w == 0.0) w = 1.0;
+    } else if (clip_mode == 2) {
+      w = fmax(w, clip_val);
+    }
+    if (window_power == 2) w = __dmul_rn(w, w);
+    p = p / (float)w;
+  }
+  return p;
+}
+
+template <bool WINDOW, int STAGES>
+__global__ void __launch_bounds__(PKF_WARPS * 32)
+pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl, const double* __restrict__ k2_tab,
+                         const double* __restrict__ sinc_tab, const double* __restrict__ thresh, double thresh_hi,
+                         int n_edges, int window_power, int clip_mode, double clip_val, double norm,
+                         int closed_last, float log2_k2min, float inv_dlog2,
+                         unsigned long long* __restrict__ counts, double* __restrict__ sums) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int nb = n_edges - 1;
+  unsigned char* s_stage = smem_raw;                                              // 16-byte aligned
+  double* s_th = reinterpret_cast<double*>(smem_raw + PKF_WARPS * STAGES * PKF_STAGE_BYTES);  // n_edges + 2
+  double* s_k2 = s_th + n_edges + 2;                                              // N
+  double* s_sinc = s_k2 + N;                                                      // N (WINDOW only)
+  double* s_sums = s_sinc + (WINDOW ? N : 0);                                     // nb
+  unsigned* s_cnt = reinterpret_cast<unsigned*>(s_sums + nb);                     // nb
+
+  for (int t = threadIdx.x; t < n_edges + 2; t += blockDim.x) {
+    double v = __longlong_as_double(0x7ff0000000000000ll);                        // +inf sentinels
+    if (t < n_edges) v = (t == n_edges - 1 && closed_last) ? thresh_hi : thresh[t];
+    s_th[t] = v;
+  }
+  for (int t = threadIdx.x; t < N; t += blockDim.x) {
+    s_k2[t] = k2_tab[t];
+    if (WINDOW) s_sinc[t] = sinc_tab[t];
+  }
+  for (int t = threadIdx.x; t < nb; t += blockDim.x) {
+    s_sums[t] = 0.0;
+    s_cnt[t] = 0u;
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nzh = N / 2 + 1;
+  const int kz_nyq = (N % 2 == 0) ? N / 2 : -1;
+  const int kz_hi = (N % 2 == 0) ? N / 2 : nzh;          // streamed range is kz = 1 .. kz_hi-1
+  const int nmain = kz_hi - 1;
+  const int nchunks = (nmain + PKF_CHUNK - 1) / PKF_CHUNK;
+  const int64_t nrows = (int64_t)N * nyl;
+  const int64_t ngroups = (nrows + 31) / 32;
+  unsigned char* my_stage = s_stage + warp * STAGES * PKF_STAGE_BYTES;
+  const unsigned my_stage_s = (unsigned)__cvta_generic_to_shared(my_stage);
+  const int ld_r = lane >> 4, ld_m = lane & 15;
+
+  for (int64_t grp = (int64_t)blockIdx.x * PKF_WARPS + warp; grp < ngroups; grp += (int64_t)gridDim.x * PKF_WARPS) {
+    const int64_t rowbase = grp * 32;
+    const int64_t row = rowbase + lane;
+    const bool active = row < nrows;
+    const int64_t rowc = active ? row : nrows - 1;
+    const int j = y0 + (int)(rowc % nyl), i = (int)(rowc / nyl);
+    const double kxy2 = __dadd_rn(s_k2[i], s_k2[j]);
+    double sxy = 1.0;
+    if (WINDOW) sxy = __dmul_rn(s_sinc[i], s_sinc[j]);
+
+    // stage issue: piece c of the 32 rows -> buffer c % STAGES (lane = 16*(row&1) + mode)
+    auto issue = [&](int c) {
+      if (c < nchunks) {
+        const int kz = 1 + c * PKF_CHUNK + ld_m;
+        if (kz < kz_hi) {
+          const unsigned dst0 = my_stage_s + (unsigned)((c % STAGES) * PKF_STAGE_BYTES + ld_m * 8);
+#pragma unroll
+          for (int t = 0; t < 16; ++t) {
+            const int r = 2 * t + ld_r;
+            int64_t gr = rowbase + r;
+            gr = gr < nrows ? gr : nrows - 1;
+            const float2* src = spec + gr * nzh + kz;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(r * PKF_PITCH)), "l"(src)
+                         : "memory");
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int c = 0; c < STAGES - 1; ++c) issue(c);
+
+    // the two weight-1 columns (generic search; every lane does this once per row)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int kz = e == 0 ? 0 : kz_nyq;
+      if (kz < 0) continue;            // warp-uniform
+      const double x = __dadd_rn(kxy2, s_k2[kz]);
+      int ge = -1;
+      float pe = 0.f;
+      if (active && x > 0.0) {
+        ge = pkf_find_bin(x, s_th, n_edges, log2_k2min, inv_dlog2);
+        if (ge >= 0 && ge < nb)
+          pe = pkf_power<WINDOW>(__ldg(spec + row * nzh + kz), sxy, WINDOW ? s_sinc[kz] : 1.0, window_power,
+                                 clip_mode, clip_val);
+      }
+      __syncwarp();
+      pkf_flush_warp(s_sums, s_cnt, nb, active && x > 0.0, ge, (double)pe, 1u, 1u, lane);
+    }
+
+    // running state of the streamed range
+    int g = nmain > 0 ? pkf_find_bin(__dadd_rn(kxy2, s_k2[1]), s_th, n_edges, log2_k2min, inv_dlog2) : nb;
+    double th1 = s_th[g + 1], th2 = s_th[g + 2];
+    double acc = 0.0;
+    unsigned cnt = 0;
+
+    for (int c = 0; c < nchunks; ++c) {
+      issue(c + STAGES - 1);
+      asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 1) : "memory");
+      __syncwarp();
+      const int kz0 = 1 + c * PKF_CHUNK;
+      const int nv = min(PKF_CHUNK, nmain - c * PKF_CHUNK);
+      const unsigned char* piece = my_stage + (c % STAGES) * PKF_STAGE_BYTES + lane * PKF_PITCH;
+      const double x_last = __dadd_rn(kxy2, s_k2[kz0 + nv - 1]);
+      bool fl_want = false;     // a closed (bin, sum, count) of the branch-free path, flushed collectively below
+      int fl_g = -1;
+      double fl_acc = 0.0;
+      unsigned fl_cnt = 0;
+      if (x_last < th2) {
+        // at most one shell boundary (th1) inside this piece: branch-free split
+        float fc = 0.f, fn = 0.f;
+        int ncur = 0;
+#pragma unroll
+        for (int mm = 0; mm < PKF_CHUNK / 2; ++mm) {
+          const float4 q = *reinterpret_cast<const float4*>(piece + mm * 16);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int m = 2 * mm + h;
+            if (m < nv) {
+              const double x = __dadd_rn(kxy2, s_k2[kz0 + m]);
+              const float2 v = h == 0 ? make_float2(q.x, q.y) : make_float2(q.z, q.w);
+              const float p = pkf_power<WINDOW>(v, sxy, WINDOW ? s_sinc[kz0 + m] : 1.0, window_power, clip_mode,
+                                                clip_val);
+              const bool cur = x < th1;
+              fc += cur ? p : 0.f;
+              fn += cur ? 0.f : p;
+              ncur += cur ? 1 : 0;
+            }
+          }
+        }
+        acc += (double)fc;
+        cnt += (unsigned)ncur;
+        if (ncur < nv) {
+          fl_want = active;
+          fl_g = g;
+          fl_acc = acc;
+          fl_cnt = cnt;
+          ++g;
+          acc = (double)fn;
+          cnt = (unsigned)(nv - ncur);
+          th1 = th2;
+          th2 = s_th[min(g + 2, n_edges + 1)];
+        }
+      } else {
+        for (int m = 0; m < nv; ++m) {
+          const double x = __dadd_rn(kxy2, s_k2[kz0 + m]);
+          const float2 v = *reinterpret_cast<const float2*>(piece + m * 8);
+          const float p = pkf_power<WINDOW>(v, sxy, WINDOW ? s_sinc[kz0 + m] : 1.0, window_power, clip_mode,
+                                            clip_val);
+          if (x >= th1) {
+            if (active) pkf_flush(s_sums, s_cnt, nb, g, acc, cnt, 2u);
+            acc = 0.0;
+            cnt = 0;
+            do {
+              ++g;
+              th1 = th2;
+              th2 = s_th[min(g + 2, n_edges + 1)];
+            } while (x >= th1);
+          }
+          acc += (double)p;
+          cnt += 1;
+        }
+      }
+      __syncwarp();   // everyone is done with this buffer before it is refilled
+      pkf_flush_warp(s_sums, s_cnt, nb, fl_want, fl_g, fl_acc, fl_cnt, 2u, lane);
+    }
+    __syncwarp();
+    pkf_flush_warp(s_sums, s_cnt, nb, active, g, acc, cnt, 2u, lane);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < nb; b += blockDim.x) {
+    const unsigned c = s_cnt[b];
+    if (c) {
+      atomicAdd(&sums[b], s_sums[b] * norm);
+      atomicAdd(&counts[b], (unsigned long long)c);
+    }
+  }
+}
+
 // Bins the half spectrum `spec` ([N][N][N/2+1]) — shared by nb_power_spectrum and the
 // slab-decomposed path.
+// NB_PK_KERNEL=1 selects the warp-per-row kernel for complex64 too (development / A-B runs)
+static bool pk_rows_enabled() {
+  static const bool on = [] { const char* e = getenv("NB_PK_KERNEL"); return !(e && atoi(e) == 1); }();
+  return on;
+}
+
 int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, int prec, const double* k2_tab,
                        const double* sinc_tab, const double* thresh, double thresh_hi, int n_edges,
                        int window_power, int clip_mode, double clip_val, double norm, int closed_last,
@@ -156,6 +437,30 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
     kern<<<nblk, PK_WARPS * 32, smem, st>>>((const double2*)spec, N, y0, nyl, k2_tab, sinc_tab, thresh, thresh_hi,
                                             n_edges, window_power, clip_mode, clip_val, norm, closed_last,
                                             log2_k2min, inv_dlog2, (unsigned long long*)counts, sums);
+  } else if (pk_rows_enabled() && N >= 4) {
+    // production path for complex64 spectra: lane-per-row streaming kernel
+    static const int stages = [] { const char* e = getenv("NB_PK_STAGES"); return e && atoi(e) == 3 ? 3 : 2; }();
+    const size_t smem2 = (size_t)PKF_WARPS * stages * PKF_STAGE_BYTES +
+                         sizeof(double) * ((size_t)n_edges + 2 + (size_t)N * (window_power ? 2 : 1) + nb) +
+                         sizeof(unsigned) * (size_t)nb;
+    NB_REQUIRE(smem2 <= 200 * 1024, "too many bins / mesh too large for the shared-memory tables");
+    const int64_t ngroups = ((int64_t)N * nyl + 31) / 32;
+    int per_sm = (int)((size_t)220 * 1024 / (smem2 + 1024));
+    per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+    int nblk2 = ctx->num_sms * per_sm;
+    const int64_t need2 = (ngroups + PKF_WARPS - 1) / PKF_WARPS;
+    if (nblk2 > need2) nblk2 = (int)need2;
+    auto launch = [&](auto kern) -> int {
+      NB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      kern<<<nblk2, PKF_WARPS * 32, smem2, st>>>((const float2*)spec, N, y0, nyl, k2_tab, sinc_tab, thresh, thresh_hi,
+                                                 n_edges, window_power, clip_mode, clip_val, norm, closed_last,
+                                                 log2_k2min, inv_dlog2, (unsigned long long*)counts, sums);
+      return NB_OK;
+    };
+    int rc2;
+    if (stages == 3) rc2 = window_power ? launch(pk_shell_bin_rows_kernel<true, 3>) : launch(pk_shell_bin_rows_kernel<false, 3>);
+    else rc2 = window_power ? launch(pk_shell_bin_rows_kernel<true, 2>) : launch(pk_shell_bin_rows_kernel<false, 2>);
+    if (rc2) return rc2;
   } else {
     auto kern = pk_shell_bin_kernel<float2, float>;
     NB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

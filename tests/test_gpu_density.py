@@ -74,6 +74,29 @@ def test_deposit_edge_cases(api):
     assert np.abs(one - restate.cic_density(pos[3:4], L, N)).max() <= 1e-15
 
 
+@pytest.mark.parametrize("L,N", [(500.0, 16), (1000.0, 48), (1000.0, 256), (500.0, 50), (123.456, 37)])
+def test_deposit_division_free_index_adversarial(api, L, N):
+    """The float32-grid deposit derives the cell index without IEEE divisions (nb_cell_split);
+    it must still equal int(p/cell) % N bit for bit: nodes, +-1..3 ulp around nodes, box edges,
+    out-of-box and negative coordinates, plus random points."""
+    rng = np.random.default_rng(11)
+    cell = L / N
+    nodes = rng.integers(0, N + 1, size=4000).astype(np.float64) * cell
+    near = nodes.copy()
+    for _ in range(3):
+        near = np.concatenate([np.nextafter(near, -np.inf), nodes, np.nextafter(near, np.inf)])[:40000]
+    extra = np.array([0.0, -0.0, L, np.nextafter(L, 0), np.nextafter(L, 2 * L), -1e-300, 1e-300, -0.3 * cell,
+                      -7.9 * cell, L + 0.25 * cell, 2 * L + 1.0, -L - 3.0, 5e-324, 1048575.5 * cell, 3e6 * cell])
+    vals = np.concatenate([near, extra, rng.random(50000) * L, rng.random(2000) * 3 * L - L])
+    vals = vals[: (vals.size // 3) * 3]
+    pos = rng.permutation(vals).reshape(-1, 3)
+    grid, idx = api.cic_density(pos, L, N, return_index=True)       # float32 grid: division-free path
+    ref_idx, _ = restate.cic_index_weight(pos, L, N)
+    assert np.array_equal(idx, ref_idx)
+    ref = restate.cic_density(pos, L, N)
+    assert nrm(grid, ref) <= TOL
+
+
 def test_cic_assign_in_place_float32_and_float64(api, snap_test1):
     pos, L, _ = snap_test1
     N = 32
