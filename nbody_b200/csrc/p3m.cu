@@ -809,6 +809,326 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// v5 — v4's pair loop on a SLIDING z-window tile.
+//
+// ncu on v4 (profiles/r1d_ncu_full_p3m_short_v4_256.txt): the tile fill is 11 % of the
+// instructions but 24 % of the stall samples (dependent global loads at 14 warps/SM), and every
+// cell re-loads all 27 neighbour cells although the next cell along z shares 18 of them.
+// v5 gives a warp a z-run of P3M5_SEG cells of one (cx,cy) column.  The tile is three regions,
+// one per z-slab (the 3x3 cells at one z), each padded to whole 32-slot groups:
+//   first cell of the run : fill the three slabs cz-1, cz, cz+1;
+//   every further cell    : subtract cs from the z of the two slabs that stay (about 13 LDS /
+//                           FADD / STS per warp; the error stays one rounding of a value < 2cs,
+//                           what neighbour-cell candidates always carried), and fill ONLY the
+//                           new slab cz+2 into the region of the evicted one;
+// i.e. 1.1 slab fills per cell instead of 3.  Phase 1 / phase 2 are v4's (p3m4_eval2, lane-
+// private queues), run region by region with one queue.  A cell whose slab does not fit a
+// region (strong clustering) is handled by v4's chunked loop over the 27 runs on the same
+// tile memory, after which the window is rebuilt.
+#define P3M5_WARPS 4
+#define P3M5_SEG 16
+
+// fill of one slab: the 9 cells (cx+ox, cy+oy, zs) as one flattened list -> tile slots
+// [0, nt) of a region, translated by (ox*cs, oy*cs, oz*cs) (offs = offtab + 3*(oz+1), run r
+// at offs[9*r ..]); pads to a multiple of 32 with far-away sentinels.
+__device__ __forceinline__ void p3m5_fill_slab(const float4* __restrict__ sorted, const int* __restrict__ roff,
+                                               const int* __restrict__ rjs, const float* __restrict__ offs,
+                                               float* __restrict__ tx, float* __restrict__ ty,
+                                               float* __restrict__ tz, int nt, int lane) {
+  for (int t0 = lane; t0 < nt + lane; t0 += 128) {   // warp-uniform trip count
+    int n[4];
+    float4 p[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int g = min(t0 + 32 * j, nt - 1);
+      int m = 0;   // largest m with roff[m] <= g  (roff[9..31] = INT_MAX)
+#pragma unroll
+      for (int s = 8; s > 0; s >>= 1) m = (roff[m + s] <= g) ? m + s : m;
+      n[j] = m;
+      p[j] = sorted[rjs[m] + (g - roff[m])];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = t0 + 32 * j;
+      if (t < nt) {
+        tx[t] = p[j].x + offs[9 * n[j]];
+        ty[t] = p[j].y + offs[9 * n[j] + 1];
+        tz[t] = p[j].z + offs[9 * n[j] + 2];
+      }
+    }
+  }
+  const int npad = (nt + 31) & ~31;
+  if (lane < npad - nt) {
+    tx[nt + lane] = 1e18f;
+    ty[nt + lane] = 0.f;
+    tz[nt + lane] = 0.f;
+  }
+}
+
+// phase 1 over the three regions (p0, p1, p2 padded slots, multiples of 32) as ONE loop over
+// their 32-slot groups — a single copy of the test loop and of the drain keeps the kernel in
+// the instruction cache (three inlined copies measured 141 ms against v4's 90 ms).
+template <int QD>
+__device__ __forceinline__ void p3m5_pass_all(const float* __restrict__ tx, const float* __restrict__ ty,
+                                              const float* __restrict__ tz, unsigned short* __restrict__ qcol,
+                                              int caps, int p0, int p1, int p2, int strm, p3m_f32x2 nxi,
+                                              p3m_f32x2 nyi, p3m_f32x2 nzi, const P3m3Packed& k, unsigned qbase,
+                                              double& ax, double& ay, double& az) {
+  unsigned qa = qbase;
+  const unsigned qfull = qbase + (QD - 8) * 64;   // a group pushes at most 8 entries per lane
+#pragma unroll 1
+  for (int r = 0; r < 3; ++r) {
+    const int vend = r * caps + (r == 0 ? p0 : (r == 1 ? p1 : p2));
+    for (int vb = r * caps + 4 * strm; vb < vend; vb += 32) {
+      p3m_f32x2 r2[4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int v = vb + 16 * j;
+        const float4 X = *reinterpret_cast<const float4*>(tx + v);
+        const float4 Y = *reinterpret_cast<const float4*>(ty + v);
+        const float4 Z = *reinterpret_cast<const float4*>(tz + v);
+        const p3m_f32x2 dx0 = p3m_add2(p3m_pack2(X.x, X.y), nxi), dx1 = p3m_add2(p3m_pack2(X.z, X.w), nxi);
+        const p3m_f32x2 dy0 = p3m_add2(p3m_pack2(Y.x, Y.y), nyi), dy1 = p3m_add2(p3m_pack2(Y.z, Y.w), nyi);
+        const p3m_f32x2 dz0 = p3m_add2(p3m_pack2(Z.x, Z.y), nzi), dz1 = p3m_add2(p3m_pack2(Z.z, Z.w), nzi);
+        r2[2 * j] = p3m_fma2(dz0, dz0, p3m_fma2(dy0, dy0, p3m_mul2(dx0, dx0)));
+        r2[2 * j + 1] = p3m_fma2(dz1, dz1, p3m_fma2(dy1, dy1, p3m_mul2(dx1, dx1)));
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int v = vb + 16 * (j >> 1) + 2 * (j & 1);
+        float r2a, r2b;
+        p3m_unpack2(r2[j], r2a, r2b);
+        if (r2a < k.rc2) { p3m_sts_u16(qa, (unsigned short)v); qa += 64; }
+        if (r2b < k.rc2) { p3m_sts_u16(qa, (unsigned short)(v + 1)); qa += 64; }
+      }
+      if (__any_sync(0xffffffffu, qa > qfull)) {
+        p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+        qa = qbase;
+      }
+    }
+  }
+  if (__any_sync(0xffffffffu, qa != qbase))
+    p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+}
+
+__device__ __forceinline__ P3m3Packed p3m_make_packed(const P3mParams& prm, float wj) {
+  P3m3Packed k;
+  const float e2 = fmaxf(prm.eps2, 1e-20f);
+  k.eps2 = p3m_pack2(e2, e2);
+  k.ws = p3m_pack2(prm.w_scale, prm.w_scale);
+  k.tiny = p3m_pack2(1e-30f, 1e-30f);
+  k.ts = p3m_pack2(prm.t_scale, prm.t_scale);
+  k.m1 = p3m_pack2(-1.f, -1.f);
+  k.one = p3m_pack2(1.f, 1.f);
+  k.wj = p3m_pack2(wj, wj);
+#pragma unroll
+  for (int d = 0; d <= P3M_DEG; ++d) k.nq[d] = p3m_pack2(-prm.coef[d], -prm.coef[d]);
+  k.rc2 = prm.rc2;
+  return k;
+}
+
+__device__ __forceinline__ void p3m5_store_acc(double* __restrict__ acc, int64_t o, double ax, double ay, double az,
+                                               double scale, int accumulate) {
+  if (accumulate) {
+    acc[3 * o] += ax * scale; acc[3 * o + 1] += ay * scale; acc[3 * o + 2] += az * scale;
+  } else {
+    acc[3 * o] = ax * scale; acc[3 * o + 1] = ay * scale; acc[3 * o + 2] = az * scale;
+  }
+}
+
+// One cell by v4's chunked loop over the flattened 27-run list (tile = the whole 3*caps slots).
+// Out of line: only cells whose slab overflows a region come here.
+template <int QD>
+__device__ __noinline__ void p3m5_cell_chunked(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                                               const int* __restrict__ perm, int ncs, int cx, int cy, int cz, int is,
+                                               int ie, const float* __restrict__ offtab,
+                                               const P3mParams* __restrict__ sprm, float* __restrict__ tx,
+                                               float* __restrict__ ty, float* __restrict__ tz, int* __restrict__ roff,
+                                               int* __restrict__ rjs, unsigned short* __restrict__ qcol, int cap,
+                                               double scale, double* __restrict__ acc, int accumulate, int i_limit) {
+  const int lane = threadIdx.x & 31, li = lane & 7, strm = lane >> 3;
+  const P3m3Packed k = p3m_make_packed(*sprm, __ldg(&sorted[0].w));
+  int my_js = 0, my_len = 0;
+  if (lane < 27) {
+    int nx = cx + lane / 9 - 1, ny = cy + (lane / 3) % 3 - 1, nz = cz + lane % 3 - 1;
+    nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+    ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+    nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+    const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+    my_js = cell_start[n];
+    my_len = cell_start[n + 1] - my_js;
+  }
+  int incl = my_len;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int up = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += up;
+  }
+  const int ncand = __shfl_sync(0xffffffffu, incl, 31);
+  __syncwarp();
+  roff[lane] = lane < 27 ? incl - my_len : 0x7fffffff;
+  rjs[lane] = my_js;
+  __syncwarp();
+  bool resident = false;
+  for (int ib = is; ib < ie; ib += 8) {
+    const int i = ib + li;
+    const int oi = i < ie ? perm[i] : 0x7fffffff;
+    const bool ivalid = oi < i_limit;
+    if (!__any_sync(0xffffffffu, ivalid)) continue;
+    float4 pi = sorted[i < ie ? i : is];
+    if (!ivalid) pi.x = 3e18f;
+    const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int first = 0; first < ncand; first += cap) {
+      const int nt = min(cap, ncand - first);
+      if (!resident) {
+        __syncwarp();   // every lane is done reading the previous chunk
+        p3m4_fill(sorted, roff, rjs, offtab, tx, ty, tz, first, nt, lane);
+      }
+      p3m4_pass<QD>(tx, ty, tz, qcol, (nt + 31) & ~31, strm, nxi, nyi, nzi, k, ax, ay, az);
+    }
+    resident = ncand <= cap;   // whole neighbourhood fits: filled once per cell
+    ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
+    az += __shfl_xor_sync(0xffffffffu, az, 8);
+    ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
+    az += __shfl_xor_sync(0xffffffffu, az, 16);
+    if (ivalid && strm == 0) p3m5_store_acc(acc, oi, ax, ay, az, scale, accumulate);
+  }
+  __syncwarp();
+}
+
+// per-warp shared memory of v5: tile (3 regions x caps slots x 3 coordinates), run table, queue
+__host__ __device__ inline size_t p3m5_warp_bytes(int caps, int qd) { return p3m4_warp_bytes(3 * caps, qd); }
+
+template <int QD>
+__global__ void __launch_bounds__(P3M5_WARPS * 32, 4)
+p3m_short_v5_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                    const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int caps) {
+  extern __shared__ __align__(16) unsigned char p3m5_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int li = lane & 7, strm = lane >> 3;
+  const int cap = 3 * caps;
+  float* offtab = reinterpret_cast<float*>(p3m5_smem);                         // 27*3 floats (96 reserved)
+  P3mParams* sprm = reinterpret_cast<P3mParams*>(offtab + 96);                 // copy for the out-of-line path
+  unsigned char* wbase = p3m5_smem + 128 * sizeof(float) + (size_t)warp * p3m5_warp_bytes(caps, QD);
+  float* tx = reinterpret_cast<float*>(wbase);
+  float* ty = tx + cap;
+  float* tz = ty + cap;
+  int* roff = reinterpret_cast<int*>(tz + cap);
+  int* rjs = roff + 32;
+  unsigned short* qcol = reinterpret_cast<unsigned short*>(rjs + 32) + lane;
+  if (threadIdx.x < 27) {
+    const int n = threadIdx.x;
+    offtab[3 * n] = (float)(n / 9 - 1) * prm.cs;
+    offtab[3 * n + 1] = (float)((n / 3) % 3 - 1) * prm.cs;
+    offtab[3 * n + 2] = (float)(n % 3 - 1) * prm.cs;
+  }
+  if (threadIdx.x == 32) *sprm = prm;
+  for (int r = 0; r < QD + 4; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
+  __syncthreads();
+  const P3m3Packed k = p3m_make_packed(prm, __ldg(&sorted[0].w));
+  const unsigned qbase = (unsigned)__cvta_generic_to_shared(qcol);
+  const float cs = prm.cs;
+
+  const int nseg = (ncs + P3M5_SEG - 1) / P3M5_SEG;
+  const int64_t col_lo = cell_lo / ncs, col_hi = (cell_hi + ncs - 1) / ncs;
+  const int64_t nunits = (col_hi - col_lo) * nseg;
+  for (int64_t u = (int64_t)blockIdx.x * P3M5_WARPS + warp; u < nunits; u += (int64_t)gridDim.x * P3M5_WARPS) {
+    const int64_t col = col_lo + u / nseg;
+    const int seg = (int)(u % nseg);
+    const int cx = (int)(col / ncs), cy = (int)(col % ncs);
+    const int zb = seg * P3M5_SEG, ze = min(ncs, zb + P3M5_SEG);
+    bool win = false;            // regions hold the slabs cz-1, cz, cz+1 of the PREVIOUS cell
+    int n0 = 0, n1 = 0, n2 = 0;  // candidates per region (region of slab zs = (zs + 3) % 3)
+    int c0 = 0, c1 = 0, c2 = 0;  // slot of the centre column's cell inside each region
+    for (int cz = zb; cz < ze; ++cz) {
+      const int64_t c = col * ncs + cz;
+      if (c < cell_lo || c >= cell_hi) { win = false; continue; }
+      const int is = cell_start[c], ie = cell_start[c + 1];
+      if (is == ie) { win = false; continue; }
+      __syncwarp();   // every lane is done with the previous cell's tile
+      if (win) {      // slide: the slabs of cz-1 and cz move one cell down in the new frame
+#pragma unroll
+        for (int d = -1; d <= 0; ++d) {
+          const int reg = (cz + d + 3) % 3;
+          const int nr = reg == 0 ? n0 : (reg == 1 ? n1 : n2);
+          float* z = tz + reg * caps;
+          for (int t = lane; t < nr; t += 32) z[t] -= cs;
+        }
+      }
+      bool fits = true;
+      for (int oz = win ? 1 : -1; oz <= 1; ++oz) {
+        const int zs = cz + oz;
+        const int reg = (zs + 3) % 3;
+        int my_js = 0, my_len = 0;
+        if (lane < 9) {
+          int nx = cx + lane / 3 - 1, ny = cy + lane % 3 - 1, nz = zs;
+          nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+          ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+          nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+          const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+          my_js = cell_start[n];
+          my_len = cell_start[n + 1] - my_js;
+        }
+        int incl = my_len;
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+          const int up = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += up;
+        }
+        const int nt = __shfl_sync(0xffffffffu, incl, 15);
+        if (nt > caps) { fits = false; break; }
+        const int cen = __shfl_sync(0xffffffffu, incl - my_len, 4);   // first slot of the centre column's cell
+        if (reg == 0) c0 = cen; else if (reg == 1) c1 = cen; else c2 = cen;
+        __syncwarp();   // the previous slab's fill is done with the run table
+        roff[lane] = lane < 9 ? incl - my_len : 0x7fffffff;
+        rjs[lane] = my_js;
+        __syncwarp();
+        if (nt > 0)
+          p3m5_fill_slab(sorted, roff, rjs, offtab + 3 * (oz + 1), tx + reg * caps, ty + reg * caps, tz + reg * caps,
+                         nt, lane);
+        if (reg == 0) n0 = nt; else if (reg == 1) n1 = nt; else n2 = nt;
+      }
+      if (!fits) {
+        p3m5_cell_chunked<QD>(sorted, cell_start, perm, ncs, cx, cy, cz, is, ie, offtab, sprm, tx, ty, tz, roff, rjs,
+                              qcol, cap, scale, acc, accumulate, i_limit);
+        win = false;
+        continue;
+      }
+      win = true;
+      __syncwarp();   // tile complete
+      const int p0 = (n0 + 31) & ~31, p1 = (n1 + 31) & ~31, p2 = (n2 + 31) & ~31;
+      const int rown = cz % 3;
+      const float* own_z = tz + rown * caps + (rown == 0 ? c0 : (rown == 1 ? c1 : c2));
+      for (int ib = is; ib < ie; ib += 8) {
+        const int i = ib + li;
+        // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+        const int oi = i < ie ? perm[i] : 0x7fffffff;
+        const bool ivalid = oi < i_limit;
+        if (!__any_sync(0xffffffffu, ivalid)) continue;
+        float4 pi = sorted[i < ie ? i : is];
+        // the i-particle takes its z from its OWN tile slot: a slab that slid twice carries
+        // (z + cs) - cs, which can differ from z by a rounding of ~1e-7 cs; reading it back keeps
+        // the self pair (and coincident points) at exactly zero separation.  x and y of the
+        // centre column are stored untranslated.
+        pi.z = own_z[min(i, ie - 1) - is];
+        if (!ivalid) pi.x = 3e18f;   // idle lanes never pass the range test (no queue traffic)
+        const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
+        double ax = 0.0, ay = 0.0, az = 0.0;
+        p3m5_pass_all<QD>(tx, ty, tz, qcol, caps, p0, p1, p2, strm, nxi, nyi, nzi, k, qbase, ax, ay, az);
+        // fold the 4 j-streams of each i-particle
+        ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
+        az += __shfl_xor_sync(0xffffffffu, az, 8);
+        ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
+        az += __shfl_xor_sync(0xffffffffu, az, 16);
+        if (ivalid && strm == 0) p3m5_store_acc(acc, oi, ax, ay, az, scale, accumulate);
+      }
+    }
+  }
+}
+
 extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
   NB_REQUIRE(ctx && ctas_per_sm >= 0 && ctas_per_sm <= 64, "ctas_per_sm must be in [0, 64]");
   ctx->p3m_ctas_per_sm = ctas_per_sm;
@@ -841,10 +1161,12 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   const int64_t ncell = cell_hi - cell_lo;
   const int64_t cap = (int64_t)ctx->num_sms * (ctx->p3m_ctas_per_sm > 0 ? ctx->p3m_ctas_per_sm : 64);
   // v4 (two-phase: test all, evaluate in-range only) is the default; NB_P3M_KERNEL selects the
-  // older kernels for A/B measurements: 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
-  // compaction, 3 = v3 packed evaluate-all, 5 = v3's loop on v4's flattened tile fill.
+  // other kernels for A/B measurements: 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
+  // compaction, 3 = v3 packed evaluate-all, 5 = v3's loop on v4's flattened tile fill, 6 = v5 (v4's
+  // pair loop on a sliding z-window tile: 10.6 vs 12.8 ms on a 256^3 glass set, but 100-113 vs 90 ms
+  // on the clustered C5 Zel'dovich set, where 16-29 % of the z-slabs overflow their tile region).
   static const int which = [] { const char* e = getenv("NB_P3M_KERNEL"); const int v = e ? atoi(e) : 4;
-                                return (v >= 1 && v <= 5) ? v : 4; }();
+                                return (v >= 1 && v <= 6) ? v : 4; }();
   if (which == 1) {
     int64_t nblk = (ncell + P3M_WARPS - 1) / P3M_WARPS;
     if (nblk > cap) nblk = cap;
@@ -857,6 +1179,20 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     if (nblk > cap) nblk = cap;
     p3m_short_v2_kernel<<<(int)nblk, P3M2_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
                                                                   cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
+  } else if (which == 6) {
+    // v5 = v4's pair loop on a sliding z-window tile (3 regions of `caps` slots)
+    static const int caps = [] { const char* e = getenv("NB_P3M_CAPS"); const int v = e ? atoi(e) : 256;
+                                 return (v >= 32 && v <= 1024) ? (v & ~31) : 256; }();
+    const size_t smem = 128 * sizeof(float) + P3M5_WARPS * p3m5_warp_bytes(caps, 64);
+    const int nseg = (ncs + P3M5_SEG - 1) / P3M5_SEG;
+    const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nseg;
+    int64_t nblk = (nunits + P3M5_WARPS - 1) / P3M5_WARPS;
+    if (nblk > cap) nblk = cap;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v5_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    p3m_short_v5_kernel<64><<<(int)nblk, P3M5_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
+                                                                      cell_lo, cell_hi, prm, scale, acc, accumulate,
+                                                                      ilim, caps);
   } else if (which == 4 || which == 5) {
     // default: queue depth 64, tile 768, 4 CTAs/SM; NB_P3M_QD=32: depth 32, tile 704, 5 CTAs/SM
     static const int qd = [] { const char* e = getenv("NB_P3M_QD"); return (e && atoi(e) == 32) ? 32 : 64; }();

@@ -33,7 +33,9 @@ for vals in rows[2:]:
 if len(sys.argv) > 2:
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(src.splitlines()))
-    hdr, data = rows[1], rows[2:]
+    hi = [i for i, r in enumerate(rows) if "Source" in r and "Instructions Executed" in r][0]
+    hdr = rows[hi]
+    data = [r for r in rows[hi + 1:] if len(r) == len(hdr) and r[hdr.index("Instructions Executed")].isdigit()]
     ia, isrc, iss = hdr.index("Instructions Executed"), hdr.index("Source"), hdr.index("# Samples")
     tot = sum(int(r[ia]) for r in data); tots = sum(int(r[iss]) for r in data)
     segs, cur = [], None
