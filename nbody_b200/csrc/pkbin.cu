@@ -226,7 +226,7 @@ __device__ __forceinline__ float pkf_power(float2 v, double sxy, double sz, int 
 }
 
 template <bool WINDOW, int STAGES>
-__global__ void __launch_bounds__(PKF_WARPS * 32)
+__global__ void __launch_bounds__(PKF_WARPS * 32, 4)
 pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl, const double* __restrict__ k2_tab,
                          const double* __restrict__ sinc_tab, const double* __restrict__ thresh, double thresh_hi,
                          int n_edges, int window_power, int clip_mode, double clip_val, double norm,
@@ -235,13 +235,13 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nb = n_edges - 1;
   unsigned char* s_stage = smem_raw;                                              // 16-byte aligned
-  double* s_th = reinterpret_cast<double*>(smem_raw + PKF_WARPS * STAGES * PKF_STAGE_BYTES);  // n_edges + 2
-  double* s_k2 = s_th + n_edges + 2;                                              // N
+  double* s_th = reinterpret_cast<double*>(smem_raw + PKF_WARPS * STAGES * PKF_STAGE_BYTES);  // n_edges + 3
+  double* s_k2 = s_th + n_edges + 3;                                              // N
   double* s_sinc = s_k2 + N;                                                      // N (WINDOW only)
   double* s_sums = s_sinc + (WINDOW ? N : 0);                                     // nb
   unsigned* s_cnt = reinterpret_cast<unsigned*>(s_sums + nb);                     // nb
 
-  for (int t = threadIdx.x; t < n_edges + 2; t += blockDim.x) {
+  for (int t = threadIdx.x; t < n_edges + 3; t += blockDim.x) {
     double v = __longlong_as_double(0x7ff0000000000000ll);                        // +inf sentinels
     if (t < n_edges) v = (t == n_edges - 1 && closed_last) ? thresh_hi : thresh[t];
     s_th[t] = v;
@@ -279,19 +279,30 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
     if (WINDOW) sxy = __dmul_rn(s_sinc[i], s_sinc[j]);
 
     // stage issue: piece c of the 32 rows -> buffer c % STAGES (lane = 16*(row&1) + mode)
+    const bool full = rowbase + 32 <= nrows;
+    const float2* src0 = spec + (rowbase + ld_r) * nzh;
+    const int64_t stride2 = 2 * (int64_t)nzh;
     auto issue = [&](int c) {
       if (c < nchunks) {
         const int kz = 1 + c * PKF_CHUNK + ld_m;
         if (kz < kz_hi) {
-          const unsigned dst0 = my_stage_s + (unsigned)((c % STAGES) * PKF_STAGE_BYTES + ld_m * 8);
+          const unsigned dst0 = my_stage_s + (unsigned)((c % STAGES) * PKF_STAGE_BYTES + ld_m * 8 + ld_r * PKF_PITCH);
+          if (full) {   // all 32 rows exist: one pointer, a constant stride of two rows
+            const float2* src = src0 + kz;
 #pragma unroll
-          for (int t = 0; t < 16; ++t) {
-            const int r = 2 * t + ld_r;
-            int64_t gr = rowbase + r;
-            gr = gr < nrows ? gr : nrows - 1;
-            const float2* src = spec + gr * nzh + kz;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(r * PKF_PITCH)), "l"(src)
-                         : "memory");
+            for (int t = 0; t < 16; ++t)
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(2 * t * PKF_PITCH)),
+                           "l"(src + (int64_t)t * stride2)
+                           : "memory");
+          } else {      // last group: clamp the row
+#pragma unroll
+            for (int t = 0; t < 16; ++t) {
+              int64_t gr = rowbase + 2 * t + ld_r;
+              gr = gr < nrows ? gr : nrows - 1;
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(2 * t * PKF_PITCH)),
+                           "l"(spec + gr * nzh + kz)
+                           : "memory");
+            }
           }
         }
       }
@@ -320,7 +331,7 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
 
     // running state of the streamed range
     int g = nmain > 0 ? pkf_find_bin(__dadd_rn(kxy2, s_k2[1]), s_th, n_edges, log2_k2min, inv_dlog2) : nb;
-    double th1 = s_th[g + 1], th2 = s_th[g + 2];
+    double th1 = s_th[g + 1], th2 = s_th[g + 2], th3 = s_th[g + 3];
     double acc = 0.0;
     unsigned cnt = 0;
 
@@ -331,15 +342,31 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
       const int kz0 = 1 + c * PKF_CHUNK;
       const int nv = min(PKF_CHUNK, nmain - c * PKF_CHUNK);
       const unsigned char* piece = my_stage + (c % STAGES) * PKF_STAGE_BYTES + lane * PKF_PITCH;
-      const double x_last = __dadd_rn(kxy2, s_k2[kz0 + nv - 1]);
-      bool fl_want = false;     // a closed (bin, sum, count) of the branch-free path, flushed collectively below
-      int fl_g = -1;
-      double fl_acc = 0.0;
-      unsigned fl_cnt = 0;
-      if (x_last < th2) {
-        // at most one shell boundary (th1) inside this piece: branch-free split
-        float fc = 0.f, fn = 0.f;
-        int ncur = 0;
+      const double* k2c = s_k2 + kz0;
+      const double x_last = __dadd_rn(kxy2, k2c[nv - 1]);
+      // up to two closed (bin, sum, count) triples of the branch-free path, flushed collectively below
+      bool flA = false, flB = false;
+      int flA_g = -1, flB_g = -1;
+      double flA_acc = 0.0, flB_acc = 0.0;
+      unsigned flA_cnt = 0, flB_cnt = 0;
+      if (x_last < th3) {
+        // at most two shell boundaries (th1 <= th2) inside this piece.  x is non-decreasing in m, so
+        // the numbers n1 / n2 of modes below th1 / th2 come from a 5-step counting search (same
+        // float64 add and compare as the per-mode test), and the 16 powers are then split by index.
+        auto count_below = [&](double th) {
+          int cb = 0;
+#pragma unroll
+          for (int sstep = PKF_CHUNK; sstep > 0; sstep >>= 1) {
+            const int t = cb + sstep;
+            if (t <= nv) {
+              if (__dadd_rn(kxy2, k2c[t - 1]) < th) cb = t;
+            }
+          }
+          return cb;
+        };
+        const int n1 = count_below(th1);
+        const int n2 = x_last >= th2 ? count_below(th2) : nv;   // (no warp collective here: lanes diverge)
+        float f1 = 0.f, f2 = 0.f, f3 = 0.f;
 #pragma unroll
         for (int mm = 0; mm < PKF_CHUNK / 2; ++mm) {
           const float4 q = *reinterpret_cast<const float4*>(piece + mm * 16);
@@ -347,29 +374,40 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
           for (int h = 0; h < 2; ++h) {
             const int m = 2 * mm + h;
             if (m < nv) {
-              const double x = __dadd_rn(kxy2, s_k2[kz0 + m]);
               const float2 v = h == 0 ? make_float2(q.x, q.y) : make_float2(q.z, q.w);
               const float p = pkf_power<WINDOW>(v, sxy, WINDOW ? s_sinc[kz0 + m] : 1.0, window_power, clip_mode,
                                                 clip_val);
-              const bool cur = x < th1;
-              fc += cur ? p : 0.f;
-              fn += cur ? 0.f : p;
-              ncur += cur ? 1 : 0;
+              const bool b1 = m < n1, b2 = m < n2;
+              f1 += b1 ? p : 0.f;
+              f2 += (!b1 && b2) ? p : 0.f;
+              f3 += b2 ? 0.f : p;
             }
           }
         }
-        acc += (double)fc;
-        cnt += (unsigned)ncur;
-        if (ncur < nv) {
-          fl_want = active;
-          fl_g = g;
-          fl_acc = acc;
-          fl_cnt = cnt;
-          ++g;
-          acc = (double)fn;
-          cnt = (unsigned)(nv - ncur);
-          th1 = th2;
-          th2 = s_th[min(g + 2, n_edges + 1)];
+        acc += (double)f1;
+        cnt += (unsigned)n1;
+        if (n1 < nv) {            // crossed th1: the running bin g is closed
+          flA = active;
+          flA_g = g;
+          flA_acc = acc;
+          flA_cnt = cnt;
+          if (n2 < nv) {          // crossed th2 as well: bin g+1 lies entirely inside this piece
+            flB = active;
+            flB_g = g + 1;
+            flB_acc = (double)f2;
+            flB_cnt = (unsigned)(n2 - n1);
+            g += 2;
+            acc = (double)f3;
+            cnt = (unsigned)(nv - n2);
+            th1 = th3;
+          } else {
+            g += 1;
+            acc = (double)f2;
+            cnt = (unsigned)(nv - n1);
+            th1 = th2;
+          }
+          th2 = s_th[min(g + 2, n_edges + 2)];
+          th3 = s_th[min(g + 3, n_edges + 2)];
         }
       } else {
         for (int m = 0; m < nv; ++m) {
@@ -384,7 +422,8 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
             do {
               ++g;
               th1 = th2;
-              th2 = s_th[min(g + 2, n_edges + 1)];
+              th2 = th3;
+              th3 = s_th[min(g + 3, n_edges + 2)];
             } while (x >= th1);
           }
           acc += (double)p;
@@ -392,7 +431,8 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
         }
       }
       __syncwarp();   // everyone is done with this buffer before it is refilled
-      pkf_flush_warp(s_sums, s_cnt, nb, fl_want, fl_g, fl_acc, fl_cnt, 2u, lane);
+      pkf_flush_warp(s_sums, s_cnt, nb, flA, flA_g, flA_acc, flA_cnt, 2u, lane);
+      if (__any_sync(0xffffffffu, flB)) pkf_flush_warp(s_sums, s_cnt, nb, flB, flB_g, flB_acc, flB_cnt, 2u, lane);
     }
     __syncwarp();
     pkf_flush_warp(s_sums, s_cnt, nb, active, g, acc, cnt, 2u, lane);
@@ -441,7 +481,7 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
     // production path for complex64 spectra: lane-per-row streaming kernel
     static const int stages = [] { const char* e = getenv("NB_PK_STAGES"); return e && atoi(e) == 3 ? 3 : 2; }();
     const size_t smem2 = (size_t)PKF_WARPS * stages * PKF_STAGE_BYTES +
-                         sizeof(double) * ((size_t)n_edges + 2 + (size_t)N * (window_power ? 2 : 1) + nb) +
+                         sizeof(double) * ((size_t)n_edges + 3 + (size_t)N * (window_power ? 2 : 1) + nb) +
                          sizeof(unsigned) * (size_t)nb;
     NB_REQUIRE(smem2 <= 200 * 1024, "too many bins / mesh too large for the shared-memory tables");
     const int64_t ngroups = ((int64_t)N * nyl + 31) / 32;
