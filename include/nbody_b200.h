@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 3
+#define NB_ABI_VERSION 4
 
 #define NB_OK 0
 #define NB_EINVAL (-1)  /* bad argument */
@@ -273,6 +273,19 @@ int nb_slab_unpack(nb_ctx* ctx, const void* src, void* dst, int nxl, int G, int 
 int nb_slab_owner(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N, int planes_per_rank,
                   int32_t* owner, int64_t* counts, int G, void* stream);
 int nb_grid_add(nb_ctx* ctx, float* dst, const float* src, int64_t n, void* stream);
+
+/* ---- batched snapshot -> delta -------------------------------------------
+ * Replaces the per-file loop of Feeder_pipe.run_frap_to_delta (TheFeedingPipeline/
+ * Feeder_pipe.py:163-195): for each of B snapshots  cic_density -> dens/dens.mean() - 1 ->
+ * ifftn(fftn(.)/W).real  [-> delta -= delta.mean() where submean[b] != 0]  (FraP_kTilDelta.py:73-127).
+ * pos: concatenated (total_particles, 3) float64 positions; offsets_dev: B+1 int64 (first particle
+ * of each snapshot, offsets[B] = total); cell_dev: B float64 cell sizes boxsize_b / N;
+ * sinc_tabs_dev: [B][N] float64 window tables of each snapshot's box; submean_dev: B int32, nullable;
+ * grids: [B][N][N][N] float32 (prec = NB_F32) or float64 (NB_F64), overwritten with delta. */
+int nb_snapshot_delta_batch(nb_ctx* ctx, const double* pos, const int64_t* offsets_dev,
+                            int64_t total_particles, int B, const double* cell_dev, int N,
+                            const double* sinc_tabs_dev, int guard, const int32_t* submean_dev,
+                            void* grids, int prec, void* stream);
 
 #ifdef __cplusplus
 }

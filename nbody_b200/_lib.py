@@ -64,6 +64,8 @@ PROTOTYPES = {
     "nb_slab_unpack": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp]),
     "nb_slab_owner": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
     "nb_grid_add": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp]),
+    "nb_snapshot_delta_batch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_i32,
+                                        c_vp]),
 }
 
 
@@ -95,7 +97,7 @@ def load():
     return lib
 
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 def check(rc: int, what: str = ""):

@@ -110,6 +110,50 @@ def snapshot_to_delta(positions, boxsize, ngrid, subtract_mean=False, precision=
     return _out(g)
 
 
+def snapshots_to_delta(positions_list, boxsizes, ngrid, subtract_mean=False, precision="f32"):
+    """Batched form of snapshot_to_delta for the snapshot corpus: every
+    snapshot of `positions_list` goes through deposit -> delta -> deconvolve [-> minus mean] in ONE
+    library call.  boxsizes: scalar or one per snapshot; subtract_mean: bool or one flag per
+    snapshot.  Returns (B, ngrid, ngrid, ngrid) float64."""
+    eng = default_engine()
+    plist = [_positions(p) for p in positions_list]
+    B = len(plist)
+    if B == 0:
+        return np.zeros((0, int(ngrid), int(ngrid), int(ngrid)))
+    offsets = np.concatenate([[0], np.cumsum([p.shape[0] for p in plist])]).astype(np.int64)
+    boxes = np.broadcast_to(np.asarray(boxsizes, dtype=np.float64), (B,)).copy()
+    flags = np.broadcast_to(np.asarray(subtract_mean, dtype=bool), (B,)).astype(np.int32)
+    pos = eng.to_device(np.concatenate(plist) if offsets[-1] else np.zeros((0, 3)))
+    g = eng.snapshot_delta_batch(pos, offsets, boxes, int(ngrid), subtract_mean=flags if flags.any() else None,
+                                 dtype=_dtype(precision))
+    return _out(g)
+
+
+def run_frap_to_delta(data_dir, ngrid, batch=64, precision="f32"):
+    """Feeder_pipe.run_frap_to_delta (TheFeedingPipeline/Feeder_pipe.py:163-195) on the GPU: same
+    directory layout in (`Test_Data_concept`, `TrainingVal_Concept`) and out (`Test data_CONCEPT/
+    delta_test_id-<i>.npy`, `Training & val data_CONCEPT/delta_train_id-<i>.npy`, float64), the
+    snapshots of each set processed `batch` at a time.  Returns the list of files written."""
+    import os
+    from . import snapshot
+    written = []
+    for sub_in, sub_out, stem, submean in (("Test_Data_concept", "Test data_CONCEPT", "delta_test_id-", False),
+                                           ("TrainingVal_Concept", "Training & val data_CONCEPT", "delta_train_id-", True)):
+        root, out = os.path.join(data_dir, sub_in), os.path.join(data_dir, sub_out)
+        os.makedirs(out, exist_ok=True)
+        files = sorted(snapshot.find_hdf5_files(root))
+        for lo in range(0, len(files), int(batch)):
+            chunk = files[lo:lo + int(batch)]
+            pos = [snapshot.read_positions(f) for f in chunk]
+            box = [snapshot.read_boxsize(f) for f in chunk]
+            deltas = snapshots_to_delta(pos, box, ngrid, subtract_mean=submean, precision=precision)
+            for k, d in enumerate(deltas):
+                path = os.path.join(out, f"{stem}{lo + k + 1}.npy")
+                np.save(path, d)
+                written.append(path)
+    return written
+
+
 # --------------------------------------------------------------------------------- a4
 def power_spectrum_from_positions(positions, L, Nmesh, deconvolve=False, use_fac=False,
                                   variant="power_compare", precision="f32", return_counts=False):

@@ -147,6 +147,34 @@ class Engine:
                                               int(bool(guard)), self.stream), "nb_deconvolve_cic")
         return grid
 
+    # -- §8f row 4: batched snapshot -> delta ----------------------------------------------
+    def snapshot_delta_batch(self, pos_cat: torch.Tensor, offsets, boxsizes, N: int, subtract_mean=None,
+                             guard: bool = True, dtype=torch.float32) -> torch.Tensor:
+        """B snapshots -> (B,N,N,N) delta in one call (Feeder_pipe.py:163-195).  pos_cat: concatenated
+        (total,3) float64 device tensor; offsets: B+1 ints; boxsizes: B floats; subtract_mean: None or
+        B flags (delta -= delta.mean() for the training/validation set, Feeder_pipe.py:193)."""
+        offsets = np.asarray(offsets, dtype=np.int64)
+        B = offsets.size - 1
+        boxsizes = np.asarray(boxsizes, dtype=np.float64).reshape(B)
+        if B < 1 or offsets[0] != 0 or np.any(np.diff(offsets) < 0) or offsets[-1] != pos_cat.shape[0]:
+            raise ValueError("offsets must start at 0, be non-decreasing and end at the particle count")
+        if pos_cat.dtype != torch.float64 or not pos_cat.is_contiguous():
+            raise ValueError("pos_cat must be a contiguous float64 (total,3) tensor")
+        N = int(N)
+        d_off = torch.from_numpy(offsets).to(self.device)
+        d_cell = torch.from_numpy(boxsizes / N).to(self.device)
+        tabs = np.stack([tables.sinc_table(N, float(L)) for L in boxsizes])
+        d_tabs = torch.from_numpy(np.ascontiguousarray(tabs)).to(self.device)
+        d_flags = None
+        if subtract_mean is not None:
+            d_flags = torch.from_numpy(np.asarray(subtract_mean, dtype=np.int32).reshape(B)).to(self.device)
+        grids = torch.empty((B, N, N, N), dtype=dtype, device=self.device)
+        _lib.check(self.lib.nb_snapshot_delta_batch(self.ctx, _ptr(pos_cat), _ptr(d_off), int(offsets[-1]), int(B),
+                                                    _ptr(d_cell), N, _ptr(d_tabs), int(bool(guard)),
+                                                    _ptr(d_flags) if d_flags is not None else None, _ptr(grids),
+                                                    _prec_of(grids), self.stream), "nb_snapshot_delta_batch")
+        return grids
+
     def sinc_tab(self, N, L, kq_form="inv_d"):
         fn = {"inv_d": tables.sinc_table, "piN_L": tables.sinc_table_kq}[kq_form]
         return self.table(("sinc", kq_form, N, float(L)), lambda: fn(N, L))

@@ -213,3 +213,49 @@ def test_full_size_properties_c2(api):
     d = grid.double()
     rhs = float(N ** 3 * (d * d).sum() - d.sum() ** 2)
     assert abs(lhs / rhs - 1) <= 1e-5
+
+
+# ------------------------------------------------------------- §8f row 4: batched snapshot -> delta
+@pytest.mark.parametrize("prec,tol", [("f32", TOL), ("f64", 1e-12)])
+def test_batched_snapshots_match_the_shipped_golden_deltas(api, prec, tol):
+    """Feeder_pipe.run_frap_to_delta as ONE library call: the four committed CONCEPT snapshots
+    (two of the test set, two of the training set with `delta -= delta.mean()`) plus a ragged
+    random set; each against the reference's own shipped delta_*.npy / the float64 oracle."""
+    tags = ["test1", "test57", "train1", "train200"]
+    gs = [golden(f"snap_{t}.npz") for t in tags]
+    rng = np.random.default_rng(3)
+    extra = rng.random((777, 3)) * 250.0
+    pos = [g["pos"] for g in gs] + [extra, np.zeros((0, 3)) + 1.0]
+    box = [float(g["boxsize"]) for g in gs] + [250.0, 250.0]
+    flags = [t.startswith("train") for t in tags] + [True, False]
+    d = api.snapshots_to_delta(pos[:5], box[:5], 32, subtract_mean=flags[:5], precision=prec)
+    assert d.shape == (5, 32, 32, 32) and d.dtype == np.float64
+    for k, g in enumerate(gs):
+        assert nrm(d[k], g["delta_golden"]) <= tol
+    ref = restate.deconvolve_cic(restate.compute_delta(restate.cic_density(extra, 250.0, 32)), 250.0, 32)
+    ref = ref - ref.mean()
+    assert nrm(d[4], ref) <= tol
+    # the batched call equals the one-snapshot call
+    one = api.snapshot_to_delta(gs[2]["pos"], box[2], 32, subtract_mean=True, precision=prec)
+    assert nrm(d[2], one) <= (1e-6 if prec == "f32" else 1e-13)
+
+
+def test_run_frap_to_delta_directory_layout(api, tmp_path, monkeypatch):
+    """Same input/output directory layout and file names as Feeder_pipe.py:163-195."""
+    from nbody_b200 import snapshot
+    gs = {t: golden(f"snap_{t}.npz") for t in ("test1", "test57", "train1")}
+    files = {"Test_Data_concept": ["a_test1.hdf5", "b_test57.hdf5"], "TrainingVal_Concept": ["a_train1.hdf5"]}
+    for sub, names in files.items():
+        (tmp_path / sub).mkdir()
+        for n in names:
+            (tmp_path / sub / n).write_bytes(b"")
+    tag_of = lambda f: f.split("_")[-1].split(".")[0]
+    monkeypatch.setattr(snapshot, "read_positions", lambda f: gs[tag_of(f)]["pos"])
+    monkeypatch.setattr(snapshot, "read_boxsize", lambda f: float(gs[tag_of(f)]["boxsize"]))
+    written = api.run_frap_to_delta(str(tmp_path), 32, batch=2)
+    assert [w.split("/")[-2:] for w in written] == [["Test data_CONCEPT", "delta_test_id-1.npy"],
+                                                    ["Test data_CONCEPT", "delta_test_id-2.npy"],
+                                                    ["Training & val data_CONCEPT", "delta_train_id-1.npy"]]
+    for w, t in zip(written, ("test1", "test57", "train1")):
+        d = np.load(w)
+        assert d.dtype == np.float64 and nrm(d, gs[t]["delta_golden"]) <= TOL

@@ -71,6 +71,23 @@ def main():
                 tmin, _ = timeit(lambda: eng.deconvolve_cic(grid, L, N), flush=flush)
                 res["deconv_total_ms"] = round(tmin, 4)
         print(json.dumps(res), flush=True)
+    if "batch" in a.ops:
+        # §8f row 4: the 300-snapshot corpus (32^3 particles on a 32^3 mesh each), one call vs 300
+        import numpy as np
+        B, n, N, Lb = 300, 32, 32, 500.0
+        pos = torch.cat([make_pos(n, Lb, "glass", seed=s) for s in range(B)])
+        off = np.arange(B + 1, dtype=np.int64) * n ** 3
+        box = np.full(B, Lb)
+        tb, _ = timeit(lambda: eng.snapshot_delta_batch(pos, off, box, N), iters=5, warm=2)
+
+        def loop():
+            for b in range(B):
+                g = eng.cic_deposit(pos[b * n ** 3:(b + 1) * n ** 3], Lb / N, N)
+                eng.compute_delta(g)
+                eng.deconvolve_cic(g, Lb, N, guard=True)
+        tl, _ = timeit(loop, iters=3, warm=1)
+        print(json.dumps({"op": "snapshot_delta_batch", "B": B, "n": n, "N": N, "batched_ms": round(tb, 3),
+                          "per_snapshot_loop_ms": round(tl, 3), "snapshots_per_s_batched": round(B / tb * 1e3, 1)}))
 
 
 if __name__ == "__main__":
