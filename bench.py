@@ -25,6 +25,9 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+_P3M_V = os.environ.get("NB_P3M_KERNEL", "4")
+P3M_KERNEL_LABEL = ("p3m_short (K5, v5: v4's pair loop on a sliding z-window tile)" if _P3M_V == "6" else
+                    f"p3m_short (K5, v{_P3M_V}: 8 i x 4 j-streams, test all / evaluate in-range)")
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
@@ -468,7 +471,7 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
                     "achieved": b / avg["kspace"] / 1e6, "alg_bytes": b})
     if "pk_bin" in avg:
         b = 8.0 * modes / world
-        hbm.append({"kernel": "pk_shell_bin (K6)", "bound": "hbm", "ms": avg["pk_bin"],
+        hbm.append({"kernel": "pk_shell_bin (K6, lane-per-row)", "bound": "hbm", "ms": avg["pk_bin"],
                     "achieved": b / avg["pk_bin"] / 1e6, "alg_bytes": b})
     for name in ("gather_kick_drift", "gather"):
         if name in phase_ms:
@@ -500,12 +503,24 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
                                             i_limit=pos.shape[0])
         t = phase_ms["p3m_short"] * 1e-3
         ach = inr * P3M_FLOP / t / 1e12
-        fp = {"kernel": "p3m_short (K5, v4: 8 i x 4 j-streams, test all / evaluate in-range)", "bound": "fp32", "ms": phase_ms["p3m_short"],
+        fp = {"kernel": P3M_KERNEL_LABEL, "bound": "fp32", "ms": phase_ms["p3m_short"],
               "achieved": ach, "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
               "flop_per_inrange_pair": P3M_FLOP, "inrange_pairs": inr, "candidate_pairs": cand,
               "candidate_pairs_per_s": cand / t,
               "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
     allk = hbm + ([fp] if fp else [])
+    # DRAM traffic per launch from the committed ncu --set full captures (profiles/ncu_traffic.json);
+    # it cannot be measured live, so it is only filled in for the exact size that was captured
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            traffic_tab = json.load(fh)["entries"]
+    except (OSError, ValueError, KeyError):
+        traffic_tab = []
+    for r in allk:
+        for e in traffic_tab:
+            if world == 1 and e["match"] in r["kernel"] and e["particles"] == n ** 3 and e["mesh"] == N:
+                r["traffic"] = float(e["bytes"])
+                r["traffic_source"] = e["source"]
     if allk:
         dom = max(allk, key=lambda r: r["ms"])
         out["roofline"] = dom
