@@ -25,9 +25,11 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-_P3M_V = os.environ.get("NB_P3M_KERNEL", "4")
-P3M_KERNEL_LABEL = ("p3m_short (K5, v5: v4's pair loop on a sliding z-window tile)" if _P3M_V == "6" else
-                    f"p3m_short (K5, v{_P3M_V}: 8 i x 4 j-streams, test all / evaluate in-range)")
+_P3M_V = os.environ.get("NB_P3M_KERNEL", "7")
+P3M_KERNEL_LABEL = {"7": "p3m_short (K5, v6: CTA tile shared by 4 z-adjacent cells, 8 i x 4 j-streams, test all / "
+                         "evaluate in-range)",
+                    "6": "p3m_short (K5, v5: v4's pair loop on a sliding z-window tile)"}.get(
+    _P3M_V, f"p3m_short (K5, v{_P3M_V}: tile per warp, 8 i x 4 j-streams, test all / evaluate in-range)")
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 

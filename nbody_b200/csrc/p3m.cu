@@ -703,7 +703,8 @@ template <bool QUEUE, int QD>
 __global__ void __launch_bounds__(P3M4_WARPS * 32, QD >= 64 ? 4 : 5)
 p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
-                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap) {
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
+                    const int* __restrict__ cell_list, const int* __restrict__ list_count) {
   extern __shared__ __align__(16) unsigned char p3m4_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int li = lane & 7, strm = lane >> 3;
@@ -739,8 +740,11 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
     for (int d = 0; d <= P3M_DEG; ++d) k.nq[d] = p3m_pack2(-prm.coef[d], -prm.coef[d]);
     k.rc2 = prm.rc2;
   }
+  // work items: the cells [cell_lo, cell_hi), or (v6's overflow pass) the cells of a device-side list
   const int64_t wstride = (int64_t)gridDim.x * P3M4_WARPS;
-  for (int64_t c = cell_lo + (int64_t)blockIdx.x * P3M4_WARPS + warp; c < cell_hi; c += wstride) {
+  const int64_t nwork = cell_list ? (int64_t)__ldg(list_count) : cell_hi - cell_lo;
+  for (int64_t wi = (int64_t)blockIdx.x * P3M4_WARPS + warp; wi < nwork; wi += wstride) {
+    const int64_t c = cell_list ? (int64_t)cell_list[wi] : cell_lo + wi;
     const int is = cell_start[c], ie = cell_start[c + 1];
     if (is == ie) continue;
     const int cz = (int)(c % ncs);
@@ -1129,6 +1133,223 @@ p3m_short_v5_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+// v6's form of p3m4_pass: tile slots [vbeg, vend) (multiples of 32) of the CTA tile, ABSOLUTE slot
+// indices in the queue — a stale queue entry then always names a slot that some earlier fill of
+// this kernel wrote (finite coordinates); window-relative indices could point at never-written
+// shared memory, and 0 * NaN in the masked accumulate is NaN.
+template <int QD>
+__device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const float* __restrict__ ty,
+                                          const float* __restrict__ tz, unsigned short* __restrict__ qcol,
+                                          int vbeg, int vend, int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
+                                          const P3m3Packed& k, double& ax, double& ay, double& az) {
+  // 32-bit shared-memory address of the next free entry of this lane's column (64 B per row)
+  const unsigned qbase = (unsigned)__cvta_generic_to_shared(qcol);
+  unsigned qa = qbase;
+  const unsigned qfull = qbase + (QD - 8) * 64;   // a group pushes at most 8 entries per lane
+  for (int vb = vbeg + 4 * strm; vb < vend; vb += 32) {
+    p3m_f32x2 r2[4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int v = vb + 16 * j;
+      const float4 X = *reinterpret_cast<const float4*>(tx + v);
+      const float4 Y = *reinterpret_cast<const float4*>(ty + v);
+      const float4 Z = *reinterpret_cast<const float4*>(tz + v);
+      const p3m_f32x2 dx0 = p3m_add2(p3m_pack2(X.x, X.y), nxi), dx1 = p3m_add2(p3m_pack2(X.z, X.w), nxi);
+      const p3m_f32x2 dy0 = p3m_add2(p3m_pack2(Y.x, Y.y), nyi), dy1 = p3m_add2(p3m_pack2(Y.z, Y.w), nyi);
+      const p3m_f32x2 dz0 = p3m_add2(p3m_pack2(Z.x, Z.y), nzi), dz1 = p3m_add2(p3m_pack2(Z.z, Z.w), nzi);
+      r2[2 * j] = p3m_fma2(dz0, dz0, p3m_fma2(dy0, dy0, p3m_mul2(dx0, dx0)));
+      r2[2 * j + 1] = p3m_fma2(dz1, dz1, p3m_fma2(dy1, dy1, p3m_mul2(dx1, dx1)));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int v = vb + 16 * (j >> 1) + 2 * (j & 1);
+      float r2a, r2b;
+      p3m_unpack2(r2[j], r2a, r2b);
+      if (r2a < k.rc2) { p3m_sts_u16(qa, (unsigned short)v); qa += 64; }
+      if (r2b < k.rc2) { p3m_sts_u16(qa, (unsigned short)(v + 1)); qa += 64; }
+    }
+    if (__any_sync(0xffffffffu, qa > qfull)) {
+      p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+      qa = qbase;
+    }
+  }
+  if (__any_sync(0xffffffffu, qa != qbase))
+    p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+}
+
+
+// ---------------------------------------------------------------------------------------
+// v6 — v4's pair loop with ONE tile per CTA shared by four z-adjacent cells.
+//
+// ncu on v4 at the C5 size (profiles/r1e_ncu_p3m_short_v4_v5_c5.txt): the per-warp tile fill is
+// 14 % of the instructions but 28 % of the stall samples, and the 13.8 KB of shared memory per
+// warp hold the kernel at 16 warps/SM.  The four warps of a v6 CTA take the cells z0..z0+3 of one
+// (cx,cy) column; the union of their neighbourhoods is 6 z-slabs of 9 cells (54 cells instead of
+// 4 x 27), loaded ONCE by all 128 threads into a tile ordered slab by slab.  The slabs w..w+2 that
+// warp w needs are then one contiguous slot range; rounding it out to whole 32-slot groups only
+// adds candidates of the slabs w-1 / w+3, which are a full cell (>= r_cut) away and fail the
+// range test like any other candidate.  Shared memory per warp drops to ~10 KB (5 CTAs/SM) and the
+// fill work per cell from 3 slabs to 1.5.  Tile coordinates are in the frame of cell z0+1
+// (|z| < 4 cs); the i-particle reads its own z back from its tile slot, so the self pair (and
+// coincident points) stay at exactly zero separation.  A run whose 54 cells do not fit the tile
+// is appended to a device-side list and handled afterwards by the v4 kernel (no host sync).
+#define P3M6_WARPS 4
+
+__host__ __device__ inline size_t p3m6_cta_bytes(int cap, int qd) {
+  return sizeof(float) * (3 * (size_t)cap + 192) + sizeof(int) * 160 +
+         P3M6_WARPS * sizeof(unsigned short) * (size_t)(qd + 4) * 32;
+}
+
+template <int QD>
+__global__ void __launch_bounds__(P3M6_WARPS * 32, 5)
+p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
+                    const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
+                    double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
+                    int* __restrict__ overflow_list, int* __restrict__ overflow_count) {
+  extern __shared__ __align__(16) unsigned char p3m6_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int li = lane & 7, strm = lane >> 3;
+  float* tx = reinterpret_cast<float*>(p3m6_smem);
+  float* ty = tx + cap;
+  float* tz = ty + cap;
+  float* offx = tz + cap;          // 64: translation of run m = 9*slab + 3*(ox+1) + (oy+1)
+  float* offy = offx + 64;
+  float* offz = offy + 64;
+  int* roff = reinterpret_cast<int*>(offz + 64);   // 64 (+1): exclusive prefix of the run lengths
+  int* rjs = roff + 80;                            // 64: first sorted slot of each run
+  int* s_tot = rjs + 64;                           // [0] total candidates
+  unsigned short* qcol = reinterpret_cast<unsigned short*>(s_tot + 16) + (size_t)warp * (QD + 4) * 32 + lane;
+  if (threadIdx.x < 64) {
+    const int m = threadIdx.x, sl = m / 9, r = m % 9;
+    offx[m] = (float)(r / 3 - 1) * prm.cs;
+    offy[m] = (float)(r % 3 - 1) * prm.cs;
+    offz[m] = (float)(sl - 2) * prm.cs;            // frame of cell z0+1: slab sl holds z0-1+sl
+  }
+  for (int r = 0; r < QD + 4; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
+  __syncthreads();
+  const P3m3Packed k = p3m_make_packed(prm, __ldg(&sorted[0].w));
+
+  const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
+  const int64_t col_lo = cell_lo / ncs, col_hi = (cell_hi + ncs - 1) / ncs;
+  const int64_t nunits = (col_hi - col_lo) * nrun;
+  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+    const int64_t col = col_lo + u / nrun;
+    const int z0 = (int)(u % nrun) * P3M6_WARPS;
+    const int cx = (int)(col / ncs), cy = (int)(col % ncs);
+    const int nact = min(P3M6_WARPS, ncs - z0);     // cells of this run
+    __syncthreads();   // every warp is done with the previous tile and run table
+    // run table: 9 cells of each of the nact+2 slabs
+    int my_len = 0;
+    if (threadIdx.x < 64) {
+      const int m = threadIdx.x, sl = m / 9, r = m % 9;
+      int js = 0;
+      if (sl < nact + 2) {
+        int nx = cx + r / 3 - 1, ny = cy + r % 3 - 1, nz = z0 - 1 + sl;
+        nx = nx < 0 ? nx + ncs : (nx >= ncs ? nx - ncs : nx);
+        ny = ny < 0 ? ny + ncs : (ny >= ncs ? ny - ncs : ny);
+        nz = nz < 0 ? nz + ncs : (nz >= ncs ? nz - ncs : nz);
+        const int64_t n = ((int64_t)nx * ncs + ny) * ncs + nz;
+        js = cell_start[n];
+        my_len = cell_start[n + 1] - js;
+      }
+      rjs[m] = js;
+      // exclusive prefix over the 64 entries: warp scan + the first warp's total
+      int incl = my_len;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+      }
+      if (m == 31) s_tot[1] = incl;
+      roff[m] = incl - my_len;    // warp-local for now
+    }
+    __syncthreads();
+    if (threadIdx.x >= 32 && threadIdx.x < 64) roff[threadIdx.x] += s_tot[1];
+    if (threadIdx.x == 63) { const int t = roff[63] + my_len; s_tot[0] = t; roff[64] = t; }
+    __syncthreads();
+    const int total = s_tot[0];
+    if (total > cap) {   // does not fit: leave the cells of this run to the v4 pass
+      if (threadIdx.x < nact) {
+        const int64_t c = col * ncs + z0 + threadIdx.x;
+        if (c >= cell_lo && c < cell_hi && cell_start[c + 1] > cell_start[c])
+          overflow_list[atomicAdd(overflow_count, 1)] = (int)c;
+      }
+      continue;
+    }
+    // cooperative fill (4 independent loads per thread and round); runs of length 0 are skipped by
+    // the search because the next run starts at the same offset
+    for (int t0 = threadIdx.x; t0 < total; t0 += 4 * P3M6_WARPS * 32) {
+      int mm[4];
+      float4 p[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int g = min(t0 + j * P3M6_WARPS * 32, total - 1);
+        int m = 0;   // largest m with roff[m] <= g; entries past the last slab equal `total`
+#pragma unroll
+        for (int sstep = 32; sstep > 0; sstep >>= 1) m = (roff[m + sstep] <= g) ? m + sstep : m;
+        mm[j] = m;
+        p[j] = sorted[rjs[m] + (g - roff[m])];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int t = t0 + j * P3M6_WARPS * 32;
+        if (t < total) {
+          tx[t] = p[j].x + offx[mm[j]];
+          ty[t] = p[j].y + offy[mm[j]];
+          tz[t] = p[j].z + offz[mm[j]];
+        }
+      }
+    }
+    {
+      const int npad = (total + 31) & ~31;
+      if ((int)threadIdx.x < npad - total) {
+        tx[total + threadIdx.x] = 1e18f;
+        ty[total + threadIdx.x] = 0.f;
+        tz[total + threadIdx.x] = 0.f;
+      }
+    }
+    __syncthreads();
+    // The i-blocks (8 particles) of the run's cells form one work list dealt round-robin to the
+    // four warps: a warp per cell would leave the CTA waiting for its most populated cell at the
+    // next barrier.  Cell w is run 4 of slab w+1, so its first slot and size come from the table.
+    int e[P3M6_WARPS + 1];
+    e[0] = 0;
+#pragma unroll
+    for (int w = 0; w < P3M6_WARPS; ++w) {
+      const int64_t cw = col * ncs + z0 + w;
+      const int m = 9 * (w + 1) + 4;
+      const int cnt = (w < nact && cw >= cell_lo && cw < cell_hi) ? roff[m + 1] - roff[m] : 0;
+      e[w + 1] = e[w] + ((cnt + 7) >> 3);
+    }
+    for (int blk = warp; blk < e[P3M6_WARPS]; blk += P3M6_WARPS) {
+      const int w = (blk >= e[1]) + (blk >= e[2]) + (blk >= e[3]);
+      const int m = 9 * (w + 1) + 4;
+      const int is = rjs[m], ie = is + (roff[m + 1] - roff[m]);
+      const int ib = is + 8 * (blk - (w == 0 ? e[0] : (w == 1 ? e[1] : (w == 2 ? e[2] : e[3]))));
+      // this cell's candidates: slabs w .. w+2, rounded out to whole groups
+      const int a_w = roff[9 * w] & ~31;
+      const int b_w = (roff[9 * (w + 3)] + 31) & ~31;
+      const float* own_z = tz + roff[m];
+      const int i = ib + li;
+      // particles with perm >= i_limit are halo copies of another slab's particles: sources only
+      const int oi = i < ie ? perm[i] : 0x7fffffff;
+      const bool ivalid = oi < i_limit;
+      if (!__any_sync(0xffffffffu, ivalid)) continue;
+      float4 pi = sorted[i < ie ? i : is];
+      pi.z = own_z[min(i, ie - 1) - is];
+      if (!ivalid) pi.x = 3e18f;   // idle lanes never pass the range test (no queue traffic)
+      const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
+      double ax = 0.0, ay = 0.0, az = 0.0;
+      p3m6_pass<QD>(tx, ty, tz, qcol, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
+      ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
+      az += __shfl_xor_sync(0xffffffffu, az, 8);
+      ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
+      az += __shfl_xor_sync(0xffffffffu, az, 16);
+      if (ivalid && strm == 0) p3m5_store_acc(acc, oi, ax, ay, az, scale, accumulate);
+    }
+  }
+}
+
 extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
   NB_REQUIRE(ctx && ctas_per_sm >= 0 && ctas_per_sm <= 64, "ctas_per_sm must be in [0, 64]");
   ctx->p3m_ctas_per_sm = ctas_per_sm;
@@ -1160,13 +1381,13 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   const int ilim = (i_limit <= 0 || i_limit > 0x7fffffff) ? 0x7fffffff : (int)i_limit;
   const int64_t ncell = cell_hi - cell_lo;
   const int64_t cap = (int64_t)ctx->num_sms * (ctx->p3m_ctas_per_sm > 0 ? ctx->p3m_ctas_per_sm : 64);
-  // v4 (two-phase: test all, evaluate in-range only) is the default; NB_P3M_KERNEL selects the
-  // other kernels for A/B measurements: 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
+  // v6 (7: v4's two-phase pair loop on one tile per CTA shared by four z-adjacent cells) is the
+  // default; NB_P3M_KERNEL selects the other kernels for A/B measurements: 4 = v4 (tile per warp), 1 = v1 warp-per-cell lanes over i, 2 = v2 lanes over j +
   // compaction, 3 = v3 packed evaluate-all, 5 = v3's loop on v4's flattened tile fill, 6 = v5 (v4's
   // pair loop on a sliding z-window tile: 10.6 vs 12.8 ms on a 256^3 glass set, but 100-113 vs 90 ms
   // on the clustered C5 Zel'dovich set, where 16-29 % of the z-slabs overflow their tile region).
-  static const int which = [] { const char* e = getenv("NB_P3M_KERNEL"); const int v = e ? atoi(e) : 4;
-                                return (v >= 1 && v <= 6) ? v : 4; }();
+  static const int which = [] { const char* e = getenv("NB_P3M_KERNEL"); const int v = e ? atoi(e) : 7;
+                                return (v >= 1 && v <= 7) ? v : 7; }();
   if (which == 1) {
     int64_t nblk = (ncell + P3M_WARPS - 1) / P3M_WARPS;
     if (nblk > cap) nblk = cap;
@@ -1179,6 +1400,33 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     if (nblk > cap) nblk = cap;
     p3m_short_v2_kernel<<<(int)nblk, P3M2_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
                                                                   cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
+  } else if (which == 7) {
+    // v6: one tile per CTA shared by four z-adjacent cells, then v4 over the runs that did not fit
+    static const int cap6 = [] { const char* e = getenv("NB_P3M_CAP6"); const int v = e ? atoi(e) : 1920;
+                                 return (v >= 256 && v <= 4096) ? (v & ~31) : 1920; }();
+    const size_t smem6 = p3m6_cta_bytes(cap6, 64);
+    void* ovf = nullptr;
+    int rc = nb_scratch(ctx, NB_SCR_SORT3, sizeof(int) * (size_t)(ncell + 4), &ovf);
+    if (rc) return rc;
+    int* ovf_count = (int*)ovf;
+    int* ovf_list = ovf_count + 4;
+    NB_CHECK_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int), st));
+    const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
+    const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nrun;
+    int64_t nblk = nunits < cap ? nunits : cap;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem6));
+    p3m_short_v6_kernel<64><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
+                                                                       cell_lo, cell_hi, prm, scale, acc, accumulate,
+                                                                       ilim, cap6, ovf_list, ovf_count);
+    NB_LAUNCHED(ctx);
+    const int tile_cap = P3M4_CAP;
+    const size_t smem4 = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, 64);
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem4));
+    p3m_short_v4_kernel<true, 64><<<ctx->num_sms * 4, P3M4_WARPS * 32, smem4, st>>>(
+        (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim,
+        tile_cap, ovf_list, ovf_count);
   } else if (which == 6) {
     // v5 = v4's pair loop on a sliding z-window tile (3 regions of `caps` slots)
     static const int caps = [] { const char* e = getenv("NB_P3M_CAPS"); const int v = e ? atoi(e) : 256;
@@ -1207,7 +1455,7 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
                                        (int)smem));                                                                  \
     p3m_short_v4_kernel<Q, D><<<(int)nblk, P3M4_WARPS * 32, smem, st>>>((const float4*)sorted_xyzw, cell_start, perm, \
                                                                         ncs, cell_lo, cell_hi, prm, scale, acc,      \
-                                                                        accumulate, ilim, tile_cap);                 \
+                                                                        accumulate, ilim, tile_cap, nullptr, nullptr); \
   } while (0)
     if (which == 4 && qd == 64) P3M4_LAUNCH(true, 64);
     else if (which == 4) P3M4_LAUNCH(true, 32);

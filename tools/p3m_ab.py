@@ -14,7 +14,7 @@ other = sys.argv[2] if len(sys.argv) > 2 else None
 eng = Engine(0)
 rs = np.random.RandomState(3)
 out = {}
-for name, L, ncs, npart, ilim_frac, half in (("u20", 100.0, 6, 6 ** 3 * 20, 1.0, False), ("halo", 100.0, 5, 5 ** 3 * 14, 0.8, True),
+for name, L, ncs, npart, ilim_frac, half in (("u20", 100.0, 6, 6 ** 3 * 20, 1.0, False), ("odd7", 100.0, 7, 7 ** 3 * 25, 1.0, False), ("clump", 100.0, 9, 9 ** 3 * 12, 0.9, True), ("halo", 100.0, 5, 5 ** 3 * 14, 0.8, True),
                                        ("dense", 100.0, 5, 5 ** 3 * 40, 1.0, False), ("big", 100.0, 40, 40 ** 3 * 22, 1.0, False)):
     pos = rs.uniform(0, L, size=(npart, 3))
     if half:
@@ -33,7 +33,7 @@ for name, L, ncs, npart, ilim_frac, half in (("u20", 100.0, 6, 6 ** 3 * 20, 1.0,
 np.savez(f"gpurun_out/p3m_ab_{tag}.npz", **out)
 if other:
     o = np.load(f"gpurun_out/p3m_ab_{other}.npz")
-    for name in ("u20", "halo", "dense", "big"):
+    for name in ("u20", "odd7", "clump", "halo", "dense", "big"):
         a, b = out[name], o[name]
         d = np.abs(a - b).max(axis=1)
         rms = np.sqrt((b ** 2).mean())
