@@ -100,7 +100,7 @@ kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const doub
 
 // Fused PM tail: gather the 3 force meshes (optionally a second, interlace-shifted set,
 // averaged), kick, drift, wrap.  One pass over the particle stream.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, int x0, int nxp,
                          double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
                          const double* __restrict__ acc_add, double* __restrict__ acc_out, int64_t np,

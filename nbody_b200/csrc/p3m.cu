@@ -1137,23 +1137,34 @@ p3m_short_v5_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
 // indices in the queue — a stale queue entry then always names a slot that some earlier fill of
 // this kernel wrote (finite coordinates); window-relative indices could point at never-written
 // shared memory, and 0 * NaN in the masked accumulate is NaN.
+// The loads go through explicit 32-bit shared addresses (one running address, ty/tz at +cap4 /
+// +2*cap4 bytes): with generic pointers ptxas re-derived the three tile bases and the queue limit
+// from S2R/S2UR in every iteration (84 instructions per group, 17 of them address arithmetic).
+__device__ __forceinline__ float4 p3m_lds128(unsigned saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+
 template <int QD>
 __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const float* __restrict__ ty,
-                                          const float* __restrict__ tz, unsigned short* __restrict__ qcol,
-                                          int vbeg, int vend, int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
+                                          const float* __restrict__ tz, unsigned txs, unsigned cap4,
+                                          unsigned short* __restrict__ qcol, unsigned qbase, int vbeg, int vend,
+                                          int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
                                           const P3m3Packed& k, double& ax, double& ay, double& az) {
-  // 32-bit shared-memory address of the next free entry of this lane's column (64 B per row)
-  const unsigned qbase = (unsigned)__cvta_generic_to_shared(qcol);
   unsigned qa = qbase;
   const unsigned qfull = qbase + (QD - 8) * 64;   // a group pushes at most 8 entries per lane
-  for (int vb = vbeg + 4 * strm; vb < vend; vb += 32) {
+  unsigned sx = txs + 4u * (unsigned)(vbeg + 4 * strm);
+  const unsigned send = txs + 4u * (unsigned)vend;
+  int v0 = vbeg + 4 * strm;
+  for (; sx < send; sx += 128u, v0 += 32) {
+    const unsigned sy = sx + cap4, sz = sy + cap4;
     p3m_f32x2 r2[4];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      const int v = vb + 16 * j;
-      const float4 X = *reinterpret_cast<const float4*>(tx + v);
-      const float4 Y = *reinterpret_cast<const float4*>(ty + v);
-      const float4 Z = *reinterpret_cast<const float4*>(tz + v);
+      const float4 X = p3m_lds128(sx + 64u * j);
+      const float4 Y = p3m_lds128(sy + 64u * j);
+      const float4 Z = p3m_lds128(sz + 64u * j);
       const p3m_f32x2 dx0 = p3m_add2(p3m_pack2(X.x, X.y), nxi), dx1 = p3m_add2(p3m_pack2(X.z, X.w), nxi);
       const p3m_f32x2 dy0 = p3m_add2(p3m_pack2(Y.x, Y.y), nyi), dy1 = p3m_add2(p3m_pack2(Y.z, Y.w), nyi);
       const p3m_f32x2 dz0 = p3m_add2(p3m_pack2(Z.x, Z.y), nzi), dz1 = p3m_add2(p3m_pack2(Z.z, Z.w), nzi);
@@ -1162,7 +1173,7 @@ __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const fl
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int v = vb + 16 * (j >> 1) + 2 * (j & 1);
+      const int v = v0 + 16 * (j >> 1) + 2 * (j & 1);
       float r2a, r2b;
       p3m_unpack2(r2[j], r2a, r2b);
       if (r2a < k.rc2) { p3m_sts_u16(qa, (unsigned short)v); qa += 64; }
@@ -1176,7 +1187,6 @@ __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const fl
   if (__any_sync(0xffffffffu, qa != qbase))
     p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
 }
-
 
 // ---------------------------------------------------------------------------------------
 // v6 — v4's pair loop with ONE tile per CTA shared by four z-adjacent cells.
@@ -1228,6 +1238,8 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   for (int r = 0; r < QD + 4; ++r) qcol[r * 32] = 0;   // stale reads must be valid tile indices
   __syncthreads();
   const P3m3Packed k = p3m_make_packed(prm, __ldg(&sorted[0].w));
+  const unsigned txs = (unsigned)__cvta_generic_to_shared(tx), cap4 = 4u * (unsigned)cap;
+  const unsigned qbase = (unsigned)__cvta_generic_to_shared(qcol);
 
   const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
   const int64_t col_lo = cell_lo / ncs, col_hi = (cell_hi + ncs - 1) / ncs;
@@ -1340,7 +1352,7 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
       if (!ivalid) pi.x = 3e18f;   // idle lanes never pass the range test (no queue traffic)
       const p3m_f32x2 nxi = p3m_pack2(-pi.x, -pi.x), nyi = p3m_pack2(-pi.y, -pi.y), nzi = p3m_pack2(-pi.z, -pi.z);
       double ax = 0.0, ay = 0.0, az = 0.0;
-      p3m6_pass<QD>(tx, ty, tz, qcol, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
+      p3m6_pass<QD>(tx, ty, tz, txs, cap4, qcol, qbase, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
       ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
       az += __shfl_xor_sync(0xffffffffu, az, 8);
       ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);

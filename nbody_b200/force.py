@@ -93,7 +93,29 @@ class ForceStepper:
                           variant=self.pp_variant, out=acc)
         return acc
 
-    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None):
+    def _tail_to_host(self, tail, pos, mom, out_pos, out_mom, chunks=8):
+        """Run the per-particle tail kernel `tail(a, b)` chunk by chunk and copy each finished chunk of
+        pos/mom to the host buffers on a side stream, so that the device->host copies (the longest part
+        of step_host at the C5 size) start as soon as the first chunk is done."""
+        dev = self.eng.device
+        n = pos.shape[0]
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        cs = self._copy_stream
+        step = max(1, -(-n // chunks))
+        for a in range(0, n, step):
+            b = min(n, a + step)
+            tail(a, b)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            cs.wait_event(ev)
+            with torch.cuda.stream(cs):
+                out_pos[a:b].copy_(pos[a:b], non_blocking=True)
+                out_mom[a:b].copy_(mom[a:b], non_blocking=True)
+        main.wait_stream(cs)
+
+    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None):
         """Cell sort + pair kernel into a separate buffer, mesh chain, then ONE fused kernel:
         g = gather(mesh) + short; acc_out <- g and/or kick + drift.  With self.overlap the two
         parts run on two streams (mesh chain on a high-priority one)."""
@@ -124,6 +146,12 @@ class ForceStepper:
             f, fs = self.pm_mesh(pos)
         if tail_waits is not None:            # e.g. the momentum upload of step_host
             main.wait_stream(tail_waits)
+        if host_out is not None and mom is not None and acc_out is None:
+            self._tail_to_host(lambda a, b: eng.gather_kick_drift_add(f, fs, c.gridsize, c.cell, pos[a:b], mom[a:b],
+                                                                      self._acc_s[a:b], None, 1.0, kick, drift,
+                                                                      c.boxsize),
+                               pos, mom, host_out[0], host_out[1])
+            return
         eng.gather_kick_drift_add(f, fs, c.gridsize, c.cell, pos, mom, self._acc_s, acc_out, 1.0, kick, drift,
                                   c.boxsize)
 
@@ -185,10 +213,15 @@ class ForceStepper:
         if c.method == "pm":
             f, fs = self.pm_mesh(self._dpos)
             main.wait_stream(self._side)
-            self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, self._dpos, self._dmom, None, 1.0, kick, drift,
-                                       c.boxsize)
+            self._tail_to_host(lambda a, b: self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, self._dpos[a:b],
+                                                                       self._dmom[a:b], None, 1.0, kick, drift,
+                                                                       c.boxsize),
+                               self._dpos, self._dmom, out_pos, out_mom)
+            return out_pos, out_mom
         elif self.fused_tail:
-            self._p3m_fused(self._dpos, self._dmom, None, kick, drift, tail_waits=self._side)
+            self._p3m_fused(self._dpos, self._dmom, None, kick, drift, tail_waits=self._side,
+                            host_out=(out_pos, out_mom))
+            return out_pos, out_mom
         else:
             acc = self.accel(self._dpos, periodic_pp)
             main.wait_stream(self._side)
