@@ -447,8 +447,16 @@ class DistForceStepper:
             allp = torch.cat([pos, halo]) if h else pos
         self.last_halo = h
         sorted4, perm, cell_start = mk("cell_sort", lambda: self.eng.cell_sort(allp, c.boxsize, self.ncs, mass=1.0))
+        # only the sort cells that overlap this rank's x-slab can hold own (i-) particles: cells are
+        # x-major, so that is one contiguous cell range (one cell of margin on both sides)
+        lay = self.mesh.lay
+        cs = c.boxsize / self.ncs
+        cx_lo = max(0, int(math.floor(lay.x0 * c.cell / cs)) - 1)
+        cx_hi = min(self.ncs, int(math.floor((lay.x0 + lay.nxl) * c.cell / cs)) + 2)
+        plane = self.ncs * self.ncs
         mk("p3m_short", lambda: self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut,
                                                    c.eps, scale=c.G * c.mass, out=acc, accumulate=accumulate,
+                                                   cell_lo=cx_lo * plane, cell_hi=cx_hi * plane,
                                                    i_limit=pos.shape[0]))
         self.last_sorted = (sorted4, cell_start)
         return acc
