@@ -1210,8 +1210,8 @@ __host__ __device__ inline size_t p3m6_cta_bytes(int cap, int qd) {
          P3M6_WARPS * sizeof(unsigned short) * (size_t)(qd + 4) * 32;
 }
 
-template <int QD>
-__global__ void __launch_bounds__(P3M6_WARPS * 32, 5)
+template <int QD, int CTAS>
+__global__ void __launch_bounds__(P3M6_WARPS * 32, CTAS)
 p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
@@ -1414,9 +1414,12 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
                                                                   cell_lo, cell_hi, prm, scale, acc, accumulate, ilim);
   } else if (which == 7) {
     // v6: one tile per CTA shared by four z-adjacent cells, then v4 over the runs that did not fit
-    static const int cap6 = [] { const char* e = getenv("NB_P3M_CAP6"); const int v = e ? atoi(e) : 1920;
-                                 return (v >= 256 && v <= 4096) ? (v & ~31) : 1920; }();
-    const size_t smem6 = p3m6_cta_bytes(cap6, 64);
+    // default: queue depth 56 and a 1664-slot tile -> 6 CTAs/SM at 80 registers (77.6 ms at C5);
+    // NB_P3M_V6=5: queue depth 64, 1920-slot tile, 5 CTAs/SM (80.2 ms)
+    static const int six = [] { const char* e = getenv("NB_P3M_V6"); return !(e && atoi(e) == 5); }();
+    static const int cap6 = [] { const char* e = getenv("NB_P3M_CAP6"); const int d = six ? 1664 : 1920;
+                                 const int v = e ? atoi(e) : d; return (v >= 256 && v <= 4096) ? (v & ~31) : d; }();
+    const size_t smem6 = p3m6_cta_bytes(cap6, six ? 56 : 64);
     void* ovf = nullptr;
     int rc = nb_scratch(ctx, NB_SCR_SORT3, sizeof(int) * (size_t)(ncell + 4), &ovf);
     if (rc) return rc;
@@ -1426,11 +1429,19 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
     const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nrun;
     int64_t nblk = nunits < cap ? nunits : cap;
-    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem6));
-    p3m_short_v6_kernel<64><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>((const float4*)sorted_xyzw, cell_start, perm, ncs,
-                                                                       cell_lo, cell_hi, prm, scale, acc, accumulate,
-                                                                       ilim, cap6, ovf_list, ovf_count);
+    if (six) {
+      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<56, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem6));
+      p3m_short_v6_kernel<56, 6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, cap6,
+          ovf_list, ovf_count);
+    } else {
+      NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem6));
+      p3m_short_v6_kernel<64, 5><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, cap6,
+          ovf_list, ovf_count);
+    }
     NB_LAUNCHED(ctx);
     const int tile_cap = P3M4_CAP;
     const size_t smem4 = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, 64);
