@@ -57,6 +57,7 @@ kspace_fused_kernel(const float2* __restrict__ rho1, const float2* __restrict__ 
     const float pcxy = s_pc[i] * s_pc[j] - s_ps[i] * s_ps[j];
     const float psxy = s_pc[i] * s_ps[j] + s_ps[i] * s_pc[j];
     const int64_t base = row * nzh;
+#pragma unroll 2
     for (int kz = lane; kz < nzh; kz += 32) {
       const int64_t o = base + kz;
       float2 r = rho1[o];
@@ -101,7 +102,8 @@ static int kspace_launch(nb_ctx* ctx, const void* rho1, const void* rho2, int N,
   const int64_t nspec = (int64_t)N * nyl * (N / 2 + 1);
   const size_t smem = 5 * sizeof(float) * (size_t)N;
   NB_CHECK_CUDA(cudaFuncSetAttribute(kspace_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int nblk = ctx->num_sms * 4;
+  static const int ks_ctas = [] { const char* e = getenv("NB_KS_CTAS"); const int v = e ? atoi(e) : 8; return v >= 1 && v <= 16 ? v : 8; }();
+  int nblk = ctx->num_sms * ks_ctas;
   const int64_t need = ((int64_t)N * nyl + KS_WARPS - 1) / KS_WARPS;
   if (nblk > need) nblk = (int)need;
   float2* g = (float2*)g3;
