@@ -233,3 +233,140 @@ def find_hdf5_files(root):
             if fname.endswith(".hdf5"):
                 files.append(os.path.join(d, fname))
     return sorted(files)
+
+
+# ------------------------------------------------------------------------------------------
+# writer: the same subset of HDF5 the reader walks, laid out like the files
+# CONCEPT/h5py wrote for the reference (superblock v0, old-style groups = B-tree + local heap +
+# symbol node, v1 object headers, contiguous little-endian datasets).  Differences from those
+# files: string attributes are fixed-length (class 3) instead of variable-length, and no padding
+# NIL messages are written.
+_F64_TYPE = bytes.fromhex("11203f000800000000004000340b0034ff030000")      # IEEE f64 LE, 20 bytes
+_I64_TYPE = bytes.fromhex("100800000800000000004000")                      # signed 64-bit LE, 12 bytes
+_SCALAR_SPACE = bytes.fromhex("0100000000000000")
+_LEAF_K, _INTERNAL_K = 4, 16
+
+
+def _pad8(b: bytes) -> bytes:
+    return b + b"\0" * (-len(b) % 8)
+
+
+def _attr_message(name, value):
+    if isinstance(value, str):
+        raw = value.encode("utf-8") + b"\0"
+        dt = struct.pack("<BBBBI", 0x13, 0x10, 0, 0, len(raw))                 # fixed string, UTF-8
+        data = raw
+    elif isinstance(value, (int, np.integer)) and not isinstance(value, bool):
+        dt, data = _I64_TYPE, struct.pack("<q", int(value))
+    else:
+        dt, data = _F64_TYPE, struct.pack("<d", float(value))
+    nm = name.encode("utf-8") + b"\0"
+    body = struct.pack("<BBHHH", 1, 0, len(nm), len(dt), len(_SCALAR_SPACE))
+    body += _pad8(nm) + _pad8(dt) + _pad8(_SCALAR_SPACE) + data
+    return 0x0C, 0, _pad8(body)
+
+
+def _object_header(messages):
+    body = b"".join(struct.pack("<HHB3x", t, len(b), f) + b for t, f, b in messages)
+    return struct.pack("<BBHII4x", 1, 0, len(messages), 1, len(body)) + body
+
+
+class _Writer:
+    def __init__(self):
+        self.blocks = []          # (offset, bytes)
+        self.end = 96             # superblock
+
+    def alloc(self, size):
+        off = self.end
+        self.end += (size + 7) & ~7
+        return off
+
+    def put(self, off, data):
+        self.blocks.append((off, data))
+
+    def group(self, children, attrs=()):
+        """children: {name: object header address}.  Returns (header address, btree, heap)."""
+        names = sorted(children, key=lambda s: s.encode("utf-8"))
+        if len(names) > 2 * _LEAF_K:
+            raise ValueError("too many links for one symbol node")
+        heap_data, offs = bytearray(8), {}
+        for nm in names:
+            offs[nm] = len(heap_data)
+            heap_data += _pad8(nm.encode("utf-8") + b"\0")
+        if len(heap_data) < 24:                       # room for one free-list entry like libhdf5 leaves
+            heap_data += bytes(24 - len(heap_data))
+        a_hdr_size = 16 + (8 + 16) + sum(8 + len(_attr_message(k, v)[2]) for k, v in attrs)
+        a_hdr = self.alloc(a_hdr_size)
+        a_tree = self.alloc(24 + (2 * _INTERNAL_K + 1) * 8 + 2 * _INTERNAL_K * 8)
+        a_heap = self.alloc(32)
+        a_hdat = self.alloc(len(heap_data))
+        a_snod = self.alloc(8 + 2 * _LEAF_K * 40)
+        msgs = [(0x11, 0, struct.pack("<QQ", a_tree, a_heap))] + [_attr_message(k, v) for k, v in attrs]
+        self.put(a_hdr, _object_header(msgs))
+        tree = bytearray(24 + (2 * _INTERNAL_K + 1) * 8 + 2 * _INTERNAL_K * 8)
+        struct.pack_into("<4sBBHQQ", tree, 0, b"TREE", 0, 0, 1 if names else 0, _UNDEF, _UNDEF)
+        if names:
+            struct.pack_into("<QQQ", tree, 24, 0, a_snod, offs[names[-1]])
+        self.put(a_tree, bytes(tree))
+        self.put(a_heap, struct.pack("<4sB3xQQQ", b"HEAP", 0, len(heap_data), 1, a_hdat))   # 1 = no free block
+        self.put(a_hdat, bytes(heap_data))
+        snod = bytearray(8 + 2 * _LEAF_K * 40)
+        struct.pack_into("<4sBBH", snod, 0, b"SNOD", 1, 0, len(names))
+        for i, nm in enumerate(names):
+            struct.pack_into("<QQII16x", snod, 8 + 40 * i, offs[nm], children[nm], 0, 0)
+        self.put(a_snod, bytes(snod))
+        return a_hdr, a_tree, a_heap
+
+    def dataset(self, arr):
+        arr = np.ascontiguousarray(arr, dtype="<f8")
+        space = struct.pack("<BBB5x", 1, arr.ndim, 1) + b"".join(struct.pack("<Q", d) for d in arr.shape) * 2
+        a_data = self.alloc(arr.nbytes)
+        msgs = [(0x01, 0, _pad8(space)), (0x03, 1, _pad8(_F64_TYPE)), (0x05, 1, bytes.fromhex("0201020100000000")),
+                (0x08, 1, _pad8(struct.pack("<BBQQ", 3, 1, a_data, arr.nbytes)))]
+        hdr = _object_header(msgs)
+        a_hdr = self.alloc(len(hdr))
+        self.put(a_hdr, hdr)
+        self.put(a_data, arr)
+        return a_hdr
+
+    def write(self, path, root):
+        a_root, a_tree, a_heap = root
+        sb = bytearray(96)
+        sb[:8] = _SIG
+        struct.pack_into("<BBBBBBBBHHI", sb, 8, 0, 0, 0, 0, 0, 8, 8, 0, _LEAF_K, _INTERNAL_K, 0)
+        struct.pack_into("<QQQQ", sb, 24, 0, _UNDEF, self.end, _UNDEF)
+        struct.pack_into("<QQII", sb, 56, 0, a_root, 1, 0)
+        struct.pack_into("<QQ", sb, 80, a_tree, a_heap)
+        tmp = path + ".tmp"
+        with open(tmp, "wb") as f:
+            f.truncate(self.end)
+            f.write(bytes(sb))
+            for off, data in self.blocks:
+                f.seek(off)
+                f.write(data if isinstance(data, (bytes, bytearray)) else memoryview(data).cast("B"))
+        os.replace(tmp, path)
+
+
+def write_snapshot(filename, pos, mom, boxsize, a=1.0, mass=1.0, H0=None, Omega_b=None, Omega_cdm=None,
+                   units=("Mpc", "Gyr", "10¹⁰ m☉"), species="matter"):
+    """Write a snapshot with the reference files' layout: root attributes a, boxsize, H0, Ωb, Ωcdm,
+    `unit length/time/mass`; group components/matter with attributes N, mass, species and the
+    (Np,3) float64 datasets pos and mom.  read_positions / read_momenta / read_boxsize / read_attrs
+    read it back (h5py is not in this image; the layout follows the HDF5 1.x file-format
+    specification for superblock v0, see the reader)."""
+    pos = np.ascontiguousarray(pos, dtype=np.float64)
+    mom = np.ascontiguousarray(mom, dtype=np.float64)
+    if pos.ndim != 2 or pos.shape[1] != 3 or mom.shape != pos.shape:
+        raise ValueError("pos and mom must both be (Np,3)")
+    w = _Writer()
+    d_pos, d_mom = w.dataset(pos), w.dataset(mom)
+    matter, _, _ = w.group({"pos": d_pos, "mom": d_mom},
+                           attrs=[("species", species), ("mass", float(mass)), ("N", int(pos.shape[0]))])
+    comps, _, _ = w.group({species: matter})
+    root_attrs = [("unit time", units[1]), ("unit length", units[0]), ("unit mass", units[2])]
+    for key, val in (("H0", H0), ("a", a), ("boxsize", boxsize), ("Ωb", Omega_b), ("Ωcdm", Omega_cdm)):
+        if val is not None:
+            root_attrs.append((key, float(val)))
+    root = w.group({"components": comps}, attrs=root_attrs)
+    w.write(filename, root)
+    return filename

@@ -97,6 +97,9 @@ def main():
         err = np.abs(d - g).max()
         print(f"{tag}: reference fn vs shipped golden max-abs {err:.2e}")
         assert err < 1e-12
+        if tag == "test1":   # the raw CONCEPT file itself: fixture of the a14 reader test (data, not source)
+            import shutil
+            shutil.copyfile(snap, os.path.join(OUT, "snapshot_test1.hdf5"))
         np.savez(os.path.join(OUT, f"snap_{tag}.npz"), pos=pos, boxsize=box, delta_golden=g,
                  source=os.path.relpath(snap, ref_loader.REF_ROOT))
     giant = os.path.join(ref_loader.REF_ROOT, "Different_Sizes/newrun2/3giant32pm/snapshots/snapshot_a=1.00.hdf5")

@@ -1,0 +1,118 @@
+"""Host side of the time loop (nbody_b200/cosmo.py, timeloop.py): closed
+forms of the background integrals, linear-theory sanity, and the leapfrog bookkeeping driven by
+a numpy stand-in for the force step built on the float64 oracle (oracle/force.py)."""
+import math
+
+import numpy as np
+
+from nbody_b200 import timeloop
+from nbody_b200.cosmo import Cosmology, scale_factor_edges
+from nbody_b200.params import ForceConfig, G_NEWTON
+from oracle import force as oforce
+from oracle import restate
+
+
+class OracleStepper:
+    """ForceStepper.step with the oracle's accelerations (numpy arrays, returns new arrays)."""
+
+    def __init__(self, cfg):
+        self.cfg = cfg
+
+    def step(self, pos, mom, dt_kick, dt_drift):
+        acc = oforce.accel(self.cfg, pos)
+        return oforce.kick_drift(pos, mom, acc, self.cfg.boxsize, mass=self.cfg.mass, a=1.0,
+                                 dt_kick=dt_kick, dt_drift=dt_drift)
+
+
+def numpy_zeldovich(cosmo, L, n, a_begin, mass, seed, A_s=2.1e-9, n_s=0.9649, lattice_offset=0.25):
+    """Numpy restatement of timeloop.zeldovich_ics (same draws, same conventions)."""
+    pk = timeloop.linear_pk_grid(cosmo, L, n, A_s, n_s)
+    rs = np.random.RandomState(seed)
+    c1 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    c2 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    R = restate.hermitian_R(c1, c2, guard=True)
+    _, psi = restate.grf_delta_psi(pk, R, L, n)
+    psi = np.stack([p.ravel() for p in psi], axis=1)
+    d_rel = cosmo.growth(a_begin) / cosmo.growth(1.0)
+    q = restate.lattice(L, n) + lattice_offset * L / n
+    pos = (q + d_rel * psi) % L
+    mom = mass * a_begin ** 2 * float(cosmo.H(a_begin)) * cosmo.growth_rate(a_begin) * d_rel * psi
+    return pos, mom, psi, q, (c1, c2)
+
+
+def test_einstein_de_sitter_closed_forms():
+    c = Cosmology(H0=0.07, Omega_b=0.2, Omega_cdm=0.8)
+    for a in (0.02, 0.3, 1.0):
+        assert abs(c.growth(a) / a - 1) < 1e-10 and abs(c.growth_rate(a) - 1) < 1e-10
+    a0, a1 = 0.05, 0.4
+    assert abs(c.kick_factor(a0, a1) / (2 * (math.sqrt(a1) - math.sqrt(a0)) / c.H0) - 1) < 1e-12
+    assert abs(c.drift_factor(a0, a1) / (2 * (a0 ** -0.5 - a1 ** -0.5) / c.H0) - 1) < 1e-12
+    assert abs(c.cosmic_time(1.0) / (2 / (3 * c.H0)) - 1) < 1e-10
+
+
+def test_lcdm_growth_and_spectrum_sanity():
+    c = Cosmology()                      # the reference snapshots' H0, Ωb, Ωcdm attributes
+    assert abs(c.h - 0.6736) < 1e-6 and abs(c.Omega_m - 0.31377) < 1e-4
+    assert abs(c.growth(0.02) / 0.02 - 1) < 1e-4                 # matter dominated at a_begin
+    assert 0.77 < c.growth(1.0) < 0.80
+    e = 1e-4
+    f_num = (math.log(c.growth(1 + e)) - math.log(c.growth(1 - e))) / (math.log(1 + e) - math.log(1 - e))
+    assert abs(c.growth_rate(1.0) - f_num) < 1e-6
+    assert 13.5 < c.cosmic_time(1.0) < 14.1                      # Gyr
+    assert 0.78 < c.sigma_R(A_s=2.1e-9, n_s=0.9649) < 0.88       # sigma_8 of the Giant.param cosmology
+    k = np.array([0.0, 1e-3, 0.02, 1.0])
+    p = c.linear_power(k)
+    assert p[0] == 0 and p[2] > p[1] > 0 and p[2] > p[3]
+    assert abs(c.linear_power(k[1:], a=0.5) / p[1:] - (c.growth(0.5) / c.growth(1.0)) ** 2).max() < 1e-12
+
+
+def test_step_edges_and_factors_tile_the_interval():
+    c = Cosmology()
+    edges, idx = timeloop.edges_through(0.02, [1.0, 0.17, 0.01], dlna_max=0.05)
+    assert edges[0] == 0.02 and abs(edges[idx[0]] - 0.17) < 1e-15 and abs(edges[idx[1]] - 1.0) < 1e-15
+    assert np.all(np.diff(np.log(edges)) <= 0.05 + 1e-12) and np.all(np.diff(edges) > 0)
+    K, D, Kc = timeloop.leapfrog_factors(c, edges)
+    # kicks (with the last closing half-kick) and drifts each cover [a_begin, a_end] exactly once
+    assert abs((K.sum() + Kc[-1]) / c.kick_factor(0.02, 1.0) - 1) < 1e-10
+    assert abs(D.sum() / c.drift_factor(0.02, 1.0) - 1) < 1e-10
+    assert len(scale_factor_edges(0.5, 1.0, 1.0)) == 2
+
+
+def test_leapfrog_reproduces_linear_growth_with_the_oracle_force():
+    """16^3 particles, PM on the cbrt(N) mesh of the reference's .param files, a = 0.02 -> 0.2: the
+    low-k modes of the displacement field grow by D(0.2)/D(0.02) and the momenta follow
+    a^2 H f times it.  (A mesh of 2 cbrt(N) cells puts the first harmonic of the particle lattice
+    on the mesh Nyquist frequency, where the deconvolution amplifies it: the force on a perturbed
+    lattice is then 3-7x the fluid value — measured with a plane-wave displacement — so lattice
+    ICs want mesh = cbrt(N), which is what Giant.param:28-44 configures.  The lattice sits a quarter
+    of a cell off the mesh nodes: ON the nodes every particle is at the kink of the CIC weight, the
+    response to a displacement is |dx|-like instead of linear and the low modes come out 1-3 % off
+    with mode-dependent phases — measured)"""
+    c = Cosmology()
+    L, n, N = 1000.0, 16, 16
+    rho_m = 3 * c.H0 ** 2 / (8 * math.pi * G_NEWTON) * c.Omega_m
+    mass = rho_m * L ** 3 / n ** 3
+    cfg = ForceConfig(method="pm", npart=n ** 3, boxsize=L, gridsize=N, interlace=(True, True),
+                      deconvolve=(True, True), G=G_NEWTON, mass=mass)
+    a0, a1 = 0.02, 0.2
+    # A_s 100x below Giant.param's: second-order (2LPT) mode coupling, 3-4 % at a = 0.2 with the real
+    # amplitude, drops to 0.3-0.4 % and the comparison with linear theory becomes sharp
+    pos, mom, psi, q, _ = numpy_zeldovich(c, L, n, a0, mass, seed=5, A_s=2.1e-11)
+    outs = []
+    p1, m1 = timeloop.evolve(OracleStepper(cfg), c, pos, mom, scale_factor_edges(a0, a1, 0.05),
+                             on_output=lambda a, p, m: outs.append(a))
+    assert outs == [a1]
+    disp = (p1 - q + 0.5 * L) % L - 0.5 * L
+
+    def low_modes(field):                       # |k| <= 2 k_f Fourier amplitudes of a lattice field
+        fk = np.fft.fftn(field.reshape(n, n, n, 3), axes=(0, 1, 2))
+        sel = [(1, 0, 0), (0, 1, 0), (0, 0, 1), (1, 1, 0), (0, 1, 1), (1, 0, 1), (1, 1, 1), (2, 0, 0), (0, 0, 2)]
+        return np.array([fk[s] for s in sel])
+    g = c.growth(a1) / c.growth(1.0)
+    want = low_modes(psi) * g
+    got = low_modes(disp)
+    err = np.abs(got - want).max() / np.abs(want).max()
+    assert err < 0.01, err
+    want_m = low_modes(psi) * (mass * a1 ** 2 * float(c.H(a1)) * c.growth_rate(a1) * g)
+    err_m = np.abs(low_modes(m1) - want_m).max() / np.abs(want_m).max()
+    assert err_m < 0.01, err_m
