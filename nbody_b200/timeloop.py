@@ -100,8 +100,40 @@ def linear_pk_grid(cosmo: Cosmology, L, n, A_s, n_s, a=1.0):
     return pk
 
 
+def second_order_growth(cosmo: Cosmology, a):
+    """(D₂, f₂) of 2LPT in units where D₊(1) = 1: D₂ ≈ −(3/7) D₊² Ωm(a)^(−1/143),
+    f₂ = dlnD₂/dlna ≈ 2 Ωm(a)^(6/11) (Bouchet et al. 1995 fits, as used by 2LPTic-style codes)."""
+    om_a = cosmo.Omega_m / a ** 3 * (cosmo.H0 / float(cosmo.H(a))) ** 2
+    d1 = cosmo.growth(a) / cosmo.growth(1.0)
+    return -3.0 / 7.0 * d1 * d1 * om_a ** (-1.0 / 143.0), 2.0 * om_a ** (6.0 / 11.0)
+
+
+def second_order_displacement(delta, L):
+    """ψ⁽²⁾ = ∇φ⁽²⁾ on the lattice from the linear δ(q) at D₊ = 1 (device tensor (n,n,n)):
+    ∇²φ⁽¹⁾ = δ, ∇²φ⁽²⁾ = Σ_{i>j} [φ⁽¹⁾,ii φ⁽¹⁾,jj − (φ⁽¹⁾,ij)²], so that x = q + D₊ψ⁽¹⁾ + D₂ψ⁽²⁾
+    with ψ⁽¹⁾ = −∇φ⁽¹⁾ the K7 displacement.  Eight small FFTs of an IC-time field: cuFFT through
+    torch.fft, not a hot-path kernel."""
+    import torch
+    n = delta.shape[0]
+    kv = torch.as_tensor(tables.k_vals(n, L), dtype=torch.float64, device=delta.device)
+    kx, ky, kz = kv[:, None, None], kv[None, :, None], kv[None, None, :]
+    k2 = kx * kx + ky * ky + kz * kz
+    k2[0, 0, 0] = 1.0
+    phi_k = -torch.fft.fftn(delta.to(torch.float64)) / k2
+    phi_k[0, 0, 0] = 0.0
+
+    def dd(ka, kb):
+        return torch.fft.ifftn(-(ka * kb) * phi_k).real
+    pxx, pyy, pzz = dd(kx, kx), dd(ky, ky), dd(kz, kz)
+    src = pxx * pyy + pxx * pzz + pyy * pzz - dd(kx, ky) ** 2 - dd(kx, kz) ** 2 - dd(ky, kz) ** 2
+    phi2_k = -torch.fft.fftn(src) / k2
+    phi2_k[0, 0, 0] = 0.0
+    psi2 = torch.stack([torch.fft.ifftn(1j * ka * phi2_k).real for ka in (kx, ky, kz)])
+    return psi2.reshape(3, -1).t().contiguous()
+
+
 def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649, seed=None, c1=None, c2=None,
-                  engine=None, lattice_offset=0.25):
+                  engine=None, lattice_offset=0.25, lpt=1):
     """1LPT initial conditions on the device: (pos, mom) float64 (n³,3) tensors at a_begin.
     ψ(a=1) comes from nb_grf_synthesize on the particle lattice (grid nodes = lattice sites, no
     gather needed); x = q + D₊ψ (wrapped), mom = m a² H f D₊ ψ with D₊ normalised to 1 at a = 1.
@@ -109,7 +141,9 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
     mesh = cbrt(N) a particle ON a node sits at the kink of the CIC weight and the mesh force
     responds to a small displacement like |dx|, which shows up as 1-3 % errors in the growth of the
     lowest modes; a quarter spacing is smooth for both the plain and the interlaced (half-cell
-    shifted) grid.  0 gives the reference's `particle_assigment` lattice (Power_compare.py:340-345)."""
+    shifted) grid.  0 gives the reference's `particle_assigment` lattice (Power_compare.py:340-345).
+    `lpt=2` adds the second-order term D₂ψ⁽²⁾ (`realization_options['LPT']`, Giant.param:70-72; the
+    reference compares both orders in 1LPTvs2LPT/1vs2tlptplotter.py)."""
     import torch
     from . import api
     from .engine import default_engine
@@ -117,15 +151,24 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
     n = int(n)
     pk = linear_pk_grid(cosmo, L, n, A_s, n_s, a=1.0)
     c1, c2 = api._draws(n, c1, c2, seed)
-    _, psi = eng.grf_synthesize(eng.to_device(pk), eng.to_device(c1), eng.to_device(c2), float(L), n, True,
-                                dtype=torch.float64, want_delta=False, want_psi=True)
+    if lpt not in (1, 2):
+        raise ValueError("lpt must be 1 or 2")
+    delta, psi = eng.grf_synthesize(eng.to_device(pk), eng.to_device(c1), eng.to_device(c2), float(L), n, True,
+                                    dtype=torch.float64, want_delta=(lpt == 2), want_psi=True)
     psi = psi.reshape(3, -1).t().contiguous()                       # (n³,3), lattice order (i,j,k)
     d_rel = cosmo.growth(a_begin) / cosmo.growth(1.0)
     lat = (torch.arange(n, device=eng.device, dtype=torch.float64) + float(lattice_offset)) * (float(L) / n)
     pos = torch.stack(torch.meshgrid(lat, lat, lat, indexing="ij"), -1).reshape(-1, 3).contiguous()
-    eng.displace_wrap(pos, (psi * d_rel).contiguous(), float(L))
-    mom = (psi * (mass * a_begin ** 2 * float(cosmo.H(a_begin)) * cosmo.growth_rate(a_begin) * d_rel)).contiguous()
-    return pos, mom
+    vel = mass * a_begin ** 2 * float(cosmo.H(a_begin))
+    disp = psi * d_rel
+    mom = psi * (vel * cosmo.growth_rate(a_begin) * d_rel)
+    if lpt == 2:
+        d2, f2 = second_order_growth(cosmo, a_begin)
+        psi2 = second_order_displacement(delta, float(L))
+        disp = disp + psi2 * d2
+        mom = mom + psi2 * (vel * f2 * d2)
+    eng.displace_wrap(pos, disp.contiguous(), float(L))
+    return pos, mom.contiguous()
 
 
 def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_max=0.025, output_dir=None,
@@ -156,8 +199,9 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
     eng = engine or default_engine()
     cfg.a = 1.0
     stepper = F.ForceStepper(cfg, eng)
+    lpt = int((vals.get("realization_options") or {}).get("LPT", 1))
     pos, mom = zeldovich_ics(cosmo, cfg.boxsize, n, cfg.a_begin, cfg.mass, A_s=float(prim.get("A_s", 2.1e-9)),
-                             n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng)
+                             n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt)
     edges, idx = edges_through(cfg.a_begin, output_times, dlna_max)
     results = []
 

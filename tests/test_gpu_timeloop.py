@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from test_timeloop_cpu import OracleStepper, numpy_zeldovich
+from test_timeloop_cpu import OracleStepper, numpy_second_order, numpy_zeldovich
 
 pytestmark = pytest.mark.gpu
 
@@ -38,6 +38,28 @@ def test_zeldovich_ics_match_the_numpy_restatement():
     # the reference's own lattice (no offset) is available too
     pos0, _ = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lattice_offset=0.0)
     assert _pdiff(pos0.cpu().numpy(), (pos_ref - 0.25 * L / n) % L, L) <= 1e-10 * L
+
+
+def test_second_order_ics_match_the_numpy_restatement():
+    from nbody_b200 import timeloop
+    from nbody_b200.cosmo import Cosmology
+    from oracle import restate
+    c = Cosmology()
+    L, n, a0 = 1000.0, 16, 0.1
+    cfg = _physical_cfg("pm", n, n, L, c)
+    pos1, mom1, _psi, _q, (c1, c2) = numpy_zeldovich(c, L, n, a0, cfg.mass, seed=21)
+    delta, _ = restate.grf_delta_psi(timeloop.linear_pk_grid(c, L, n, 2.1e-9, 0.9649),
+                                     restate.hermitian_R(c1, c2, guard=True), L, n)
+    psi2 = numpy_second_order(delta, L)
+    d2, f2 = timeloop.second_order_growth(c, a0)
+    pos_ref = (pos1 + d2 * psi2) % L
+    mom_ref = mom1 + cfg.mass * a0 ** 2 * float(c.H(a0)) * f2 * d2 * psi2
+    pos, mom = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lpt=2)
+    assert np.abs(d2 * psi2).max() > 1e-4                      # the term is there
+    assert _pdiff(pos.cpu().numpy(), pos_ref, L) <= 1e-10 * L
+    assert np.abs(mom.cpu().numpy() - mom_ref).max() <= 1e-10 * np.abs(mom_ref).max()
+    with pytest.raises(ValueError):
+        timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lpt=3)
 
 
 @pytest.mark.parametrize("method,n,steps", [("pm", 16, 12), ("p3m", 20, 6)])
