@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 4
+#define NB_ABI_VERSION 5
 
 #define NB_OK 0
 #define NB_EINVAL (-1)  /* bad argument */
@@ -204,6 +204,19 @@ int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy,
 int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
                 double eps, double box, double scale, int variant, int accumulate, double* acc,
                 void* stream);
+
+/* ---- K4e  periodic PP with Ewald summation ----------------------------------
+ * No reference source (CONCEPT PP gravity in a periodic box: softened nearest-image force plus a
+ * tabulated Ewald correction; method of Hernquist, Bouchet & Suto 1991).
+ * nb_ewald_table: C(d) = F_periodic(d) - d/|d|^3 on the (g+1)^3 nodes of the octant [0, box/2]^3,
+ *   splitting parameter alpha (2/box is the usual choice), images |n| <= nreal, wave vectors
+ *   |m| <= nfour.  table_f64: (g+1)^3 x 3 doubles and/or table_f4: (g+1)^3 float4 (x,y,z,0).
+ * nb_pp_accel_ewald: nb_pp_accel with box > 0 plus the trilinear interpolation of table_f4. */
+int nb_ewald_table(nb_ctx* ctx, double box, int g, double alpha, int nreal, int nfour, double* table_f64,
+                   void* table_f4, void* stream);
+int nb_pp_accel_ewald(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
+                      double eps, double box, double scale, const void* table_f4, int g, int accumulate,
+                      double* acc, void* stream);
 
 /* ---- K5  P3M short range -------------------------------------------------------------------
  * No reference source (CONCEPT-internal; log lines 42-46, 89-95 show tiling + reordering).

@@ -66,6 +66,8 @@ PROTOTYPES = {
     "nb_grid_add": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp]),
     "nb_snapshot_delta_batch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_i32,
                                         c_vp]),
+    "nb_ewald_table": (c_i32, [c_vp, c_f64, c_i32, c_f64, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "nb_pp_accel_ewald": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64, c_vp, c_i32, c_i32, c_vp, c_vp]),
 }
 
 
@@ -97,7 +99,7 @@ def load():
     return lib
 
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 
 def check(rc: int, what: str = ""):

@@ -331,6 +331,40 @@ class Engine:
                                         int(bool(accumulate)), _ptr(out), self.stream), "nb_pp_accel")
         return out
 
+    # -- K4e: periodic PP with Ewald summation ------------------------------------------
+    def ewald_table(self, box: float, g: int = 64, alpha_box: float = 2.0, nreal: int = 4, nfour: int = 5,
+                    want_f64: bool = False):
+        """Device Ewald-correction table for a box (cached per (box, g, alpha)): float4 (g+1)^3 nodes
+        for nb_pp_accel_ewald; with want_f64 also the (g+1,g+1,g+1,3) float64 values."""
+        key = ("ewald", float(box), int(g), float(alpha_box), int(nreal), int(nfour))
+        if not hasattr(self, "_ewald_tables"):
+            self._ewald_tables = {}
+        if key not in self._ewald_tables or (want_f64 and self._ewald_tables[key][1] is None):
+            g1 = int(g) + 1
+            t4 = torch.empty((g1 ** 3, 4), dtype=torch.float32, device=self.device)
+            t8 = torch.empty((g1, g1, g1, 3), dtype=torch.float64, device=self.device) if want_f64 else None
+            _lib.check(self.lib.nb_ewald_table(self.ctx, float(box), int(g), float(alpha_box) / float(box), int(nreal),
+                                               int(nfour), _ptr(t8), _ptr(t4), self.stream), "nb_ewald_table")
+            self._ewald_tables[key] = (t4, t8)
+        t4, t8 = self._ewald_tables[key]
+        return (t4, t8) if want_f64 else t4
+
+    def pp_accel_ewald(self, ipos4: torch.Tensor, jpos4: torch.Tensor, eps: float, box: float, table4: torch.Tensor,
+                       g: int, scale: float = 1.0, out: torch.Tensor | None = None,
+                       accumulate: bool = False) -> torch.Tensor:
+        for t in (ipos4, jpos4):
+            if t.dtype != torch.float32 or t.dim() != 2 or t.shape[1] != 4 or not t.is_contiguous():
+                raise ValueError("packed positions must be contiguous (n,4) float32")
+        if table4.dtype != torch.float32 or table4.shape != ((int(g) + 1) ** 3, 4) or not table4.is_contiguous():
+            raise ValueError("table must be the contiguous ((g+1)^3, 4) float32 tensor of ewald_table")
+        if out is None:
+            out = torch.empty((ipos4.shape[0], 3), dtype=torch.float64, device=self.device)
+            accumulate = False
+        _lib.check(self.lib.nb_pp_accel_ewald(self.ctx, _ptr(ipos4), ipos4.shape[0], _ptr(jpos4), jpos4.shape[0],
+                                              float(eps), float(box), float(scale), _ptr(table4), int(g),
+                                              int(bool(accumulate)), _ptr(out), self.stream), "nb_pp_accel_ewald")
+        return out
+
     # -- K5 ---------------------------------------------------------------------------
     def cell_sort(self, pos: torch.Tensor, L: float, ncs: int, mass: float = 1.0):
         self._check_pos(pos)

@@ -86,9 +86,16 @@ class ForceStepper:
         return acc
 
     def pp(self, pos, acc, periodic=False):
+        """periodic: False (open), True (nearest image only) or "ewald" (nearest image + Ewald
+        correction table, CONCEPT's periodic PP)."""
         c = self.cfg
         half = 0.5 * c.boxsize
         p4 = self.eng.pp_pack(pos, origin=(half, half, half), mass=1.0)
+        if periodic == "ewald":
+            g = int(getattr(self, "ewald_gridsize", 64))
+            self.eng.pp_accel_ewald(p4, p4, c.eps, c.boxsize, self.eng.ewald_table(c.boxsize, g), g,
+                                    scale=c.G * c.mass, out=acc)
+            return acc
         self.eng.pp_accel(p4, p4, c.eps, box=c.boxsize if periodic else 0.0, scale=c.G * c.mass,
                           variant=self.pp_variant, out=acc)
         return acc

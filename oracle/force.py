@@ -129,6 +129,90 @@ def pp_accel(pos, L=None, G=1.0, mass=1.0, eps=0.0, periodic=False, i_subset=Non
     return out
 
 
+def ewald_force(d, L, alpha_box=2.0, nreal=4, nfour=5, subtract_nearest=False):
+    """Periodic force per unit G·m on a particle from a source at separation d (M,3) (pointing to
+    the source), Ewald sum of Hernquist, Bouchet & Suto 1991:
+      Σ_n (d-nL)/|d-nL|³ [erfc(α|d-nL|) + 2α|d-nL|/√π exp(-α²|d-nL|²)]
+      + 4π/L³ Σ_{h≠0} h/h² exp(-h²/4α²) sin(h·d).
+    subtract_nearest: minus d/|d|³ of the n = 0 term (the correction the tables hold)."""
+    from scipy.special import erfc
+    d = np.atleast_2d(np.asarray(d, dtype=np.float64))
+    alpha = alpha_box / L
+    out = np.zeros_like(d)
+    rng = np.arange(-nreal, nreal + 1)
+    for nx in rng:
+        for ny in rng:
+            for nz in rng:
+                r = d - L * np.array([nx, ny, nz], dtype=np.float64)
+                r2 = (r * r).sum(-1)
+                ok = r2 > 0
+                rr = np.sqrt(np.where(ok, r2, 1.0))
+                w = (erfc(alpha * rr) + 2 * alpha * rr / math.sqrt(math.pi) * np.exp(-alpha * alpha * rr * rr)) / rr ** 3
+                if subtract_nearest and nx == 0 and ny == 0 and nz == 0:
+                    w = w - 1.0 / rr ** 3
+                out += np.where(ok, w, 0.0)[:, None] * r
+    mrng = np.arange(-nfour, nfour + 1)
+    for mx in mrng:
+        for my in mrng:
+            for mz in mrng:
+                if mx == 0 and my == 0 and mz == 0:
+                    continue
+                h = 2 * math.pi / L * np.array([mx, my, mz], dtype=np.float64)
+                h2 = (h * h).sum()
+                out += (4 * math.pi / L ** 3 * math.exp(-h2 / (4 * alpha * alpha)) / h2 * np.sin(d @ h))[:, None] * h
+    return out
+
+
+def ewald_table(L, g, alpha_box=2.0, nreal=4, nfour=5):
+    """(g+1,g+1,g+1,3) correction table on the octant [0, L/2]³.  The component odd in a coordinate
+    is exactly zero on that coordinate's plane through the origin (NOT on the far face d = L/2: the
+    periodic force vanishes there, so the correction equals minus the nearest-image term)."""
+    x = np.arange(g + 1) * (0.5 * L / g)
+    X, Y, Z = np.meshgrid(x, x, x, indexing="ij")
+    d = np.stack([X.ravel(), Y.ravel(), Z.ravel()], axis=1)
+    t = ewald_force(d, L, alpha_box, nreal, nfour, subtract_nearest=True).reshape(g + 1, g + 1, g + 1, 3)
+    t[0, :, :, 0] = 0.0
+    t[:, 0, :, 1] = 0.0
+    t[:, :, 0, 2] = 0.0
+    return t
+
+
+def ewald_correction(d, L, table):
+    """Trilinear interpolation of the octant table at nearest-image separations d (...,3): the value
+    the pair kernel adds to the softened nearest-image force."""
+    g = table.shape[0] - 1
+    u = np.minimum(np.abs(d) * (2.0 * g / L), g)
+    c = np.minimum(u.astype(np.int64), g - 1)
+    t = u - c
+    cx, cy, cz = c[..., 0], c[..., 1], c[..., 2]
+    tx, ty, tz = t[..., 0:1], t[..., 1:2], t[..., 2:3]
+
+    def at(ox, oy, oz):
+        return table[cx + ox, cy + oy, cz + oz]
+    c00 = at(0, 0, 0) + tz * (at(0, 0, 1) - at(0, 0, 0))
+    c01 = at(0, 1, 0) + tz * (at(0, 1, 1) - at(0, 1, 0))
+    c10 = at(1, 0, 0) + tz * (at(1, 0, 1) - at(1, 0, 0))
+    c11 = at(1, 1, 0) + tz * (at(1, 1, 1) - at(1, 1, 0))
+    c0 = c00 + ty * (c01 - c00)
+    c1 = c10 + ty * (c11 - c10)
+    return (c0 + tx * (c1 - c0)) * np.where(d < 0, -1.0, 1.0)
+
+
+def pp_accel_ewald(pos, L, table, G=1.0, mass=1.0, eps=0.0, i_subset=None, chunk=64):
+    """Periodic direct sum: softened nearest-image force + interpolated Ewald correction."""
+    idx = np.arange(pos.shape[0]) if i_subset is None else np.asarray(i_subset)
+    out = np.zeros((idx.size, 3))
+    for s in range(0, idx.size, chunk):
+        ii = idx[s:s + chunk]
+        d = pos[None, :, :] - pos[ii, None, :]                 # towards the source
+        d -= L * np.round(d / L)
+        r2 = (d * d).sum(-1) + eps * eps
+        r2[r2 == 0.0] = np.inf
+        f = d * (r2 ** -1.5)[..., None] + ewald_correction(d, L, table)
+        out[s:s + chunk] = G * mass * f.sum(1)
+    return out
+
+
 def p3m_short_accel(pos, L, r_s, r_cut, G=1.0, mass=1.0, eps=0.0, i_subset=None, chunk=128):
     """Short-range pair acceleration, minimum image, r < r_cut:
        a_i = -G m Σ_j r_ij / (r²+ε²)^{3/2} · split_factor(r)."""
