@@ -1491,10 +1491,14 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     // v6: one tile per CTA shared by four z-adjacent cells, then v4 over the runs that did not fit
     // default: queue depth 56 and a 1664-slot tile -> 6 CTAs/SM at 80 registers (77.6 ms at C5);
     // NB_P3M_V6=5: queue depth 64, 1920-slot tile, 5 CTAs/SM (80.2 ms)
-    static const int six = [] { const char* e = getenv("NB_P3M_V6"); return !(e && atoi(e) == 5); }();
-    static const int cap6 = [] { const char* e = getenv("NB_P3M_CAP6"); const int d = six ? 1664 : 1920;
+    // NB_P3M_V6=48: queue depth 48, 1888-slot tile, 6 CTAs/SM (fewer overflowing runs, more flushes)
+    static const int v6mode = [] { const char* e = getenv("NB_P3M_V6"); const int v = e ? atoi(e) : 0;
+                                   return v == 5 ? 64 : v == 48 ? 48 : 56; }();
+    static const int six = v6mode != 64;
+    static const int cap6 = [] { const char* e = getenv("NB_P3M_CAP6");
+                                 const int d = v6mode == 64 ? 1920 : v6mode == 48 ? 1888 : 1664;
                                  const int v = e ? atoi(e) : d; return (v >= 256 && v <= 4096) ? (v & ~31) : d; }();
-    const size_t smem6 = p3m6_cta_bytes(cap6, six ? 56 : 64);
+    const size_t smem6 = p3m6_cta_bytes(cap6, v6mode);
     void* ovf = nullptr;
     int rc = nb_scratch(ctx, NB_SCR_SORT3, sizeof(int) * (size_t)(ncell + 4), &ovf);
     if (rc) return rc;
@@ -1517,6 +1521,7 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
         ovf_list, ovf_count);                                                                                         \
   } while (0)
     if (six && maskq) P3M6_LAUNCH(56, 6, true);
+    else if (v6mode == 48) P3M6_LAUNCH(48, 6, false);
     else if (six) P3M6_LAUNCH(56, 6, false);
     else if (maskq) P3M6_LAUNCH(64, 5, true);
     else P3M6_LAUNCH(64, 5, false);
