@@ -143,13 +143,13 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const do
 // the mapping by 90 degrees: a LANE owns one (kx,ky) row and walks it along kz, so the
 // monotone bin index becomes a running register (g, next two thresholds) and a partial sum
 // stays in registers until the row crosses a shell boundary (about every 27 modes at the C5
-// size).  The 32 rows of a warp are contiguous in memory; 16-mode pieces of them are staged
-// through shared memory with 8-byte cp.async in a 2- or 3-deep pipeline (coalesced 128-byte row
-// segments in, conflict-free LDS.128 per lane out; row pitch 144 B), which keeps
-// ~8 KB per warp in flight.
+// size).  The 32 rows of a warp are contiguous in memory; PKF_CHUNK-mode pieces of them (8 by
+// default) are staged through shared memory with 8-byte cp.async in a 2- or 3-deep pipeline
+// (coalesced 64-byte row segments in, conflict-free LDS.128 per lane out; row pitch 80 B): 4 KB
+// per warp in flight, 20 warps per SM.
 //   * kz = 1 .. N/2-1 (weight 2) is the streamed range; the two weight-1 columns kz = 0 and
 //     kz = N/2 are binned by a generic search at the start of each row;
-//   * a 16-mode piece with at most one shell boundary is summed branch-free into a "current"
+//   * a piece with at most one shell boundary is summed branch-free into a "current"
 //     and a "next" float accumulator (x < th1 selects); pieces with more boundaries (low |k|
 //     only) take a per-mode loop;
 //   * partial sums are flushed into ONE shared histogram per CTA (native u32 atomics for the
@@ -157,9 +157,14 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const do
 //     to global memory once, scaled by `norm`, at the end.
 // Bin decisions use the same float64 k² tables and thresholds as above: counts stay bit-exact.
 #define PKF_WARPS 4
-#define PKF_CHUNK 16
+#ifndef PKF_CHUNK
+#define PKF_CHUNK 8            // modes per staged row piece (r1h A/B at 1024^3: 16 / 4 CTAs 1.81 ms, 8 / 5 CTAs 1.39 ms, 8 / 6 CTAs 2.14 ms)
+#endif
 #define PKF_PITCH (PKF_CHUNK * 8 + 16)          // bytes per staged row piece
 #define PKF_STAGE_BYTES (32 * PKF_PITCH)
+#ifndef PKF_MIN_CTAS
+#define PKF_MIN_CTAS 5         // 96 registers: 20 warps per SM
+#endif
 
 __device__ __forceinline__ int pkf_find_bin(double x, const double* __restrict__ s_th, int n_edges,
                                             float log2_k2min, float inv_dlog2) {
@@ -226,7 +231,7 @@ __device__ __forceinline__ float pkf_power(float2 v, double sxy, double sz, int 
 }
 
 template <bool WINDOW, int STAGES>
-__global__ void __launch_bounds__(PKF_WARPS * 32, 4)
+__global__ void __launch_bounds__(PKF_WARPS * 32, PKF_MIN_CTAS)
 pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl, const double* __restrict__ k2_tab,
                          const double* __restrict__ sinc_tab, const double* __restrict__ thresh, double thresh_hi,
                          int n_edges, int window_power, int clip_mode, double clip_val, double norm,
@@ -266,7 +271,9 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
   const int64_t ngroups = (nrows + 31) / 32;
   unsigned char* my_stage = s_stage + warp * STAGES * PKF_STAGE_BYTES;
   const unsigned my_stage_s = (unsigned)__cvta_generic_to_shared(my_stage);
-  const int ld_r = lane >> 4, ld_m = lane & 15;
+  constexpr int RPI = 32 / PKF_CHUNK;          // rows covered by one cp.async step of the warp
+  static_assert(PKF_CHUNK == 8 || PKF_CHUNK == 16 || PKF_CHUNK == 32, "PKF_CHUNK: 8, 16 or 32");
+  const int ld_r = lane / PKF_CHUNK, ld_m = lane % PKF_CHUNK;
 
   for (int64_t grp = (int64_t)blockIdx.x * PKF_WARPS + warp; grp < ngroups; grp += (int64_t)gridDim.x * PKF_WARPS) {
     const int64_t rowbase = grp * 32;
@@ -278,28 +285,28 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
     double sxy = 1.0;
     if (WINDOW) sxy = __dmul_rn(s_sinc[i], s_sinc[j]);
 
-    // stage issue: piece c of the 32 rows -> buffer c % STAGES (lane = 16*(row&1) + mode)
+    // stage issue: piece c of the 32 rows -> buffer c % STAGES (lane = PKF_CHUNK*(row % RPI) + mode)
     const bool full = rowbase + 32 <= nrows;
     const float2* src0 = spec + (rowbase + ld_r) * nzh;
-    const int64_t stride2 = 2 * (int64_t)nzh;
+    const int64_t stride2 = RPI * (int64_t)nzh;
     auto issue = [&](int c) {
       if (c < nchunks) {
         const int kz = 1 + c * PKF_CHUNK + ld_m;
         if (kz < kz_hi) {
           const unsigned dst0 = my_stage_s + (unsigned)((c % STAGES) * PKF_STAGE_BYTES + ld_m * 8 + ld_r * PKF_PITCH);
-          if (full) {   // all 32 rows exist: one pointer, a constant stride of two rows
+          if (full) {   // all 32 rows exist: one pointer, a constant stride of RPI rows
             const float2* src = src0 + kz;
 #pragma unroll
-            for (int t = 0; t < 16; ++t)
-              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(2 * t * PKF_PITCH)),
+            for (int t = 0; t < PKF_CHUNK; ++t)
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
                            "l"(src + (int64_t)t * stride2)
                            : "memory");
           } else {      // last group: clamp the row
 #pragma unroll
-            for (int t = 0; t < 16; ++t) {
-              int64_t gr = rowbase + 2 * t + ld_r;
+            for (int t = 0; t < PKF_CHUNK; ++t) {
+              int64_t gr = rowbase + RPI * t + ld_r;
               gr = gr < nrows ? gr : nrows - 1;
-              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(2 * t * PKF_PITCH)),
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
                            "l"(spec + gr * nzh + kz)
                            : "memory");
             }
@@ -486,7 +493,7 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
     NB_REQUIRE(smem2 <= 200 * 1024, "too many bins / mesh too large for the shared-memory tables");
     const int64_t ngroups = ((int64_t)N * nyl + 31) / 32;
     int per_sm = (int)((size_t)220 * 1024 / (smem2 + 1024));
-    per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+    per_sm = per_sm < 1 ? 1 : (per_sm > PKF_MIN_CTAS ? PKF_MIN_CTAS : per_sm);
     int nblk2 = ctx->num_sms * per_sm;
     const int64_t need2 = (ngroups + PKF_WARPS - 1) / PKF_WARPS;
     if (nblk2 > need2) nblk2 = (int)need2;
