@@ -107,7 +107,8 @@ int nb_deconvolve_cic(nb_ctx* ctx, void* grid, int N, int prec, const double* si
  * Plotter.py:176-202, 1vs2tlptplotter.py:96-116) and compute_power_spectrum
  * (Power_compare.py:422-465, CiC/3D startbetingelser1.py:274-315, Plotter.py:294-333):
  * R2C FFT of delta, P = |delta_k|^2 * norm / W^window_power, binned over k>0.
- * k2_tab[N]      = k_vals**2 (float64, host-computed: (2*pi*fftfreq)**2)
+ * k2_tab[N]      = k_vals**2 (float64, host-computed: (2*pi*fftfreq)**2); k2_tab and sinc_tab are even in the
+ *                  FFT index (tab[N-m] == tab[m], exact for fftfreq) and the complex64 kernel reads tab[0..N/2] only
  * thresh[n_edges]= for every bin edge e the smallest float64 x with sqrt(x) >= e, so that
  *                  "sqrt((kx²+ky²)+kz²) >= e" is decided exactly without a device sqrt
  * closed_last    = 1: np.histogram semantics (k == last edge counted in the last bin);

@@ -162,6 +162,11 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const do
 #endif
 #define PKF_PITCH (PKF_CHUNK * 8 + 16)          // bytes per staged row piece
 #define PKF_STAGE_BYTES (32 * PKF_PITCH)
+// L2 sector promotion of the staged row pieces: a 64-byte piece is half of a 128-byte line whose other half
+// is the next piece of the same row
+#ifndef PKF_L2HINT
+#define PKF_L2HINT ""            // ".L2::128B" measured: no difference (1.3250 vs 1.3246 ms)
+#endif
 #ifndef PKF_MIN_CTAS
 #define PKF_MIN_CTAS 5         // 96 registers: 20 warps per SM
 #endif
@@ -241,9 +246,12 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
   const int nb = n_edges - 1;
   unsigned char* s_stage = smem_raw;                                              // 16-byte aligned
   double* s_th = reinterpret_cast<double*>(smem_raw + PKF_WARPS * STAGES * PKF_STAGE_BYTES);  // n_edges + 3
-  double* s_k2 = s_th + n_edges + 3;                                              // N
-  double* s_sinc = s_k2 + N;                                                      // N (WINDOW only)
-  double* s_sums = s_sinc + (WINDOW ? N : 0);                                     // nb
+  // k² and the sinc factor are even in the FFT index (fftfreq: k[N-m] = -k[m] exactly), so only the
+  // entries 0 .. N/2 are kept (4 KB instead of 8 KB at N = 1024) and kx, ky fold with min(m, N-m)
+  const int nfold = N / 2 + 1;
+  double* s_k2 = s_th + n_edges + 3;                                              // nfold
+  double* s_sinc = s_k2 + nfold;                                                  // nfold (WINDOW only)
+  double* s_sums = s_sinc + (WINDOW ? nfold : 0);                                 // nb
   unsigned* s_cnt = reinterpret_cast<unsigned*>(s_sums + nb);                     // nb
 
   for (int t = threadIdx.x; t < n_edges + 3; t += blockDim.x) {
@@ -251,7 +259,7 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
     if (t < n_edges) v = (t == n_edges - 1 && closed_last) ? thresh_hi : thresh[t];
     s_th[t] = v;
   }
-  for (int t = threadIdx.x; t < N; t += blockDim.x) {
+  for (int t = threadIdx.x; t < nfold; t += blockDim.x) {
     s_k2[t] = k2_tab[t];
     if (WINDOW) s_sinc[t] = sinc_tab[t];
   }
@@ -275,12 +283,36 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
   static_assert(PKF_CHUNK == 8 || PKF_CHUNK == 16 || PKF_CHUNK == 32, "PKF_CHUNK: 8, 16 or 32");
   const int ld_r = lane / PKF_CHUNK, ld_m = lane % PKF_CHUNK;
 
-  for (int64_t grp = (int64_t)blockIdx.x * PKF_WARPS + warp; grp < ngroups; grp += (int64_t)gridDim.x * PKF_WARPS) {
+  // Work units.  Every warp takes `rounds` whole groups (32 rows, all of kz); the ngroups % nwarps groups
+  // left over would cost a full extra round for a few warps (1024^3 on 2960 warps: 11.07 -> 12 rounds), so
+  // each of them is cut along kz into `pieces` chunk ranges that are spread over all warps instead.
+  const int64_t nwarps = (int64_t)gridDim.x * PKF_WARPS;
+  const int64_t wid = (int64_t)blockIdx.x * PKF_WARPS + warp;
+  const int64_t rounds = ngroups / nwarps;
+  const int64_t left = ngroups - rounds * nwarps;
+  int pieces = 1;
+  if (left > 0) pieces = (int)min((int64_t)max(nchunks, 1), nwarps / left);
+  const int64_t tail_units = left * pieces;
+  for (int64_t it = 0; it <= rounds; ++it) {
+    int64_t grp;
+    int c_lo = 0, c_hi = nchunks;
+    bool first = true;
+    if (it < rounds) {
+      grp = wid + it * nwarps;
+    } else {
+      if (wid >= tail_units) break;
+      grp = rounds * nwarps + wid / pieces;
+      const int pc = (int)(wid % pieces);
+      c_lo = (int)((int64_t)pc * nchunks / pieces);
+      c_hi = (int)((int64_t)(pc + 1) * nchunks / pieces);
+      first = pc == 0;
+    }
     const int64_t rowbase = grp * 32;
     const int64_t row = rowbase + lane;
     const bool active = row < nrows;
     const int64_t rowc = active ? row : nrows - 1;
-    const int j = y0 + (int)(rowc % nyl), i = (int)(rowc / nyl);
+    const int jj = y0 + (int)(rowc % nyl), ii = (int)(rowc / nyl);
+    const int j = min(jj, N - jj), i = min(ii, N - ii);
     const double kxy2 = __dadd_rn(s_k2[i], s_k2[j]);
     double sxy = 1.0;
     if (WINDOW) sxy = __dmul_rn(s_sinc[i], s_sinc[j]);
@@ -290,7 +322,7 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
     const float2* src0 = spec + (rowbase + ld_r) * nzh;
     const int64_t stride2 = RPI * (int64_t)nzh;
     auto issue = [&](int c) {
-      if (c < nchunks) {
+      if (c < c_hi) {
         const int kz = 1 + c * PKF_CHUNK + ld_m;
         if (kz < kz_hi) {
           const unsigned dst0 = my_stage_s + (unsigned)((c % STAGES) * PKF_STAGE_BYTES + ld_m * 8 + ld_r * PKF_PITCH);
@@ -298,7 +330,7 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
             const float2* src = src0 + kz;
 #pragma unroll
             for (int t = 0; t < PKF_CHUNK; ++t)
-              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
+              asm volatile("cp.async.ca.shared.global" PKF_L2HINT " [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
                            "l"(src + (int64_t)t * stride2)
                            : "memory");
           } else {      // last group: clamp the row
@@ -306,7 +338,7 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
             for (int t = 0; t < PKF_CHUNK; ++t) {
               int64_t gr = rowbase + RPI * t + ld_r;
               gr = gr < nrows ? gr : nrows - 1;
-              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
+              asm volatile("cp.async.ca.shared.global" PKF_L2HINT " [%0], [%1], 8;" ::"r"(dst0 + (unsigned)(RPI * t * PKF_PITCH)),
                            "l"(spec + gr * nzh + kz)
                            : "memory");
             }
@@ -316,13 +348,13 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
 #pragma unroll
-    for (int c = 0; c < STAGES - 1; ++c) issue(c);
+    for (int c = 0; c < STAGES - 1; ++c) issue(c_lo + c);
 
     // the two weight-1 columns (generic search; every lane does this once per row)
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
       const int kz = e == 0 ? 0 : kz_nyq;
-      if (kz < 0) continue;            // warp-uniform
+      if (kz < 0 || !first) continue;  // warp-uniform
       const double x = __dadd_rn(kxy2, s_k2[kz]);
       int ge = -1;
       float pe = 0.f;
@@ -337,12 +369,12 @@ pk_shell_bin_rows_kernel(const float2* __restrict__ spec, int N, int y0, int nyl
     }
 
     // running state of the streamed range
-    int g = nmain > 0 ? pkf_find_bin(__dadd_rn(kxy2, s_k2[1]), s_th, n_edges, log2_k2min, inv_dlog2) : nb;
+    int g = c_lo < c_hi ? pkf_find_bin(__dadd_rn(kxy2, s_k2[1 + c_lo * PKF_CHUNK]), s_th, n_edges, log2_k2min, inv_dlog2) : nb;
     double th1 = s_th[g + 1], th2 = s_th[g + 2], th3 = s_th[g + 3];
     double acc = 0.0;
     unsigned cnt = 0;
 
-    for (int c = 0; c < nchunks; ++c) {
+    for (int c = c_lo; c < c_hi; ++c) {
       issue(c + STAGES - 1);
       asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 1) : "memory");
       __syncwarp();
@@ -488,7 +520,7 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
     // production path for complex64 spectra: lane-per-row streaming kernel
     static const int stages = [] { const char* e = getenv("NB_PK_STAGES"); return e && atoi(e) == 3 ? 3 : 2; }();
     const size_t smem2 = (size_t)PKF_WARPS * stages * PKF_STAGE_BYTES +
-                         sizeof(double) * ((size_t)n_edges + 3 + (size_t)N * (window_power ? 2 : 1) + nb) +
+                         sizeof(double) * ((size_t)n_edges + 3 + (size_t)(N / 2 + 1) * (window_power ? 2 : 1) + nb) +
                          sizeof(unsigned) * (size_t)nb;
     NB_REQUIRE(smem2 <= 200 * 1024, "too many bins / mesh too large for the shared-memory tables");
     const int64_t ngroups = ((int64_t)N * nyl + 31) / 32;
@@ -497,6 +529,8 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
     int nblk2 = ctx->num_sms * per_sm;
     const int64_t need2 = (ngroups + PKF_WARPS - 1) / PKF_WARPS;
     if (nblk2 > need2) nblk2 = (int)need2;
+    // NB_PK_GRID: force the CTA count (tests use it to reach the split-tail path at small N)
+    if (const char* e = getenv("NB_PK_GRID")) { const int v = atoi(e); if (v >= 1 && v < nblk2) nblk2 = v; }
     auto launch = [&](auto kern) -> int {
       NB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
       kern<<<nblk2, PKF_WARPS * 32, smem2, st>>>((const float2*)spec, N, y0, nyl, k2_tab, sinc_tab, thresh, thresh_hi,

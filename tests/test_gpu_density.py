@@ -259,3 +259,20 @@ def test_run_frap_to_delta_directory_layout(api, tmp_path, monkeypatch):
     for w, t in zip(written, ("test1", "test57", "train1")):
         d = np.load(w)
         assert d.dtype == np.float64 and nrm(d, gs[t]["delta_golden"]) <= TOL
+
+
+@pytest.mark.parametrize("grid,N", [(30, 64), (11, 64), (7, 45), (1, 32)])
+def test_pk_binning_split_tail_units(api, monkeypatch, grid, N):
+    """The shell-binning kernel cuts the groups left after the last full round into kz pieces spread
+    over all warps (1024^3 on a full B200: 208 groups in 14 pieces each).  NB_PK_GRID forces a small
+    grid so that meshes of 32-64 cells reach that path — (30, 64): 8 left-over groups in 4 pieces,
+    (11, 64): 40 in 1, (7, 45): odd mesh, (1, 32): one CTA: counts stay bit-exact, P within 1e-5."""
+    monkeypatch.setenv("NB_PK_GRID", str(grid))
+    L = 700.0
+    rs = np.random.RandomState(grid * 100 + N)
+    delta = rs.normal(size=(N, N, N))
+    for fromcic in (False, True):
+        k, p, c = api.compute_power_spectrum(delta, fromcic, L=L, N=N, return_counts=True)
+        kr, pr, cr = restate.compute_power_spectrum(delta, fromcic, L, N, return_counts=True)
+        assert np.array_equal(c, cr) and np.array_equal(k, kr)
+        assert np.abs(p / pr - 1).max() <= TOL

@@ -5,7 +5,7 @@ cd "$(dirname "$0")/../nbody_b200/csrc" || exit 1
 for v in "$@"; do
   c=${v%%:*}; k=${v##*:}
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC \
-      -DPKF_MIN_CTAS=$c -DPKF_CHUNK=$k -c pkbin.cu -o pkbin.o 2>/dev/null || exit 1
+      -DPKF_MIN_CTAS=$c -DPKF_CHUNK=$k $PK_EXTRA -c pkbin.cu -o pkbin.o 2>/dev/null || exit 1
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../libnbody_b200.so *.o \
       -L/usr/local/cuda/lib64 -lcufft -Xlinker -rpath -Xlinker /usr/local/cuda/lib64 || exit 1
   (cd ../.. && timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:pk_shell_bin_rows \
