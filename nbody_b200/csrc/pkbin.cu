@@ -156,7 +156,9 @@ pk_shell_bin_kernel(const C* __restrict__ spec, int N, int y0, int nyl, const do
 //     counts, CAS-loop f64 adds for the sums — a flush happens once per ~27 modes), which goes
 //     to global memory once, scaled by `norm`, at the end.
 // Bin decisions use the same float64 k² tables and thresholds as above: counts stay bit-exact.
+#ifndef PKF_WARPS
 #define PKF_WARPS 4
+#endif
 #ifndef PKF_CHUNK
 #define PKF_CHUNK 8            // modes per staged row piece (r1h A/B at 1024^3: 16 / 4 CTAs 1.81 ms, 8 / 5 CTAs 1.39 ms, 8 / 6 CTAs 2.14 ms)
 #endif
