@@ -5,6 +5,10 @@
 // particles %= L` (Power_compare.py:356-391, CiC/3D startbetingelser1.py:137-173).
 #include "common.cuh"
 
+#ifndef GKD_MIN_CTAS
+#define GKD_MIN_CTAS 3   // fused gather+kick+drift tail at C5: no bound 14.0 ms, 4 CTAs (64 regs, 56 B spills) 10.4 ms, 3 CTAs (80 regs) 8.4 ms, 5 CTAs 15.2 ms
+#endif
+
 struct CicStencil {
   int64_t r00, r01, r10, r11;
   int k0, k1;
@@ -100,7 +104,7 @@ kick_drift_kernel(double* __restrict__ pos, double* __restrict__ mom, const doub
 
 // Fused PM tail: gather the 3 force meshes (optionally a second, interlace-shifted set,
 // averaged), kick, drift, wrap.  One pass over the particle stream.
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, GKD_MIN_CTAS)
 gather_kick_drift_kernel(const float* __restrict__ f1, const float* __restrict__ f2, int N, int x0, int nxp,
                          double cell, double shift2, double* __restrict__ pos, double* __restrict__ mom,
                          const double* __restrict__ acc_add, double* __restrict__ acc_out, int64_t np,
