@@ -173,3 +173,25 @@ def test_second_order_growth_factors_and_plane_wave():
     delta = 0.4 * np.cos(2 * np.pi / L * 3 * X + 0.3)
     psi2 = timeloop.second_order_displacement(torch.from_numpy(delta), L).numpy()
     assert np.abs(psi2).max() < 1e-12
+
+
+def test_loop_argument_errors():
+    import pytest
+    c = Cosmology()
+    with pytest.raises(ValueError):
+        scale_factor_edges(0.5, 0.5)
+    with pytest.raises(ValueError):
+        timeloop.edges_through(0.5, [0.1, 0.5])                 # nothing after a_begin
+    cfg = ForceConfig(method="pm", npart=8, boxsize=10.0, gridsize=4, a=0.5)
+    with pytest.raises(ValueError):                             # the a-dependence lives in the integrals
+        timeloop.evolve(OracleStepper(cfg), c, np.zeros((8, 3)), np.zeros((8, 3)), scale_factor_edges(0.1, 0.2))
+    # outputs in the middle of the loop are synchronised copies: the loop state is not disturbed
+    cfg = ForceConfig(method="pm", npart=64, boxsize=100.0, gridsize=4, G=G_NEWTON, mass=1e3)
+    rs = np.random.RandomState(0)
+    pos, mom = rs.random_sample((64, 3)) * 100.0, rs.normal(size=(64, 3))
+    edges = scale_factor_edges(0.1, 0.2, 0.1)
+    seen = []
+    a = timeloop.evolve(OracleStepper(cfg), c, pos, mom, edges, output_at=[1, 3],
+                        on_output=lambda s, p, m: seen.append(s))
+    b = timeloop.evolve(OracleStepper(cfg), c, pos, mom, edges)
+    assert len(seen) == 3 and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
