@@ -75,6 +75,19 @@ def evolve(stepper, cosmo: Cosmology, pos, mom, a_edges, output_at=(), on_output
     return pos, mom
 
 
+class PeriodicPP:
+    """Adapter for a `pp` ForceStepper inside the comoving loop: the box is periodic, so every step
+    uses the nearest-image force plus the Ewald correction table (CONCEPT's periodic PP gravity)."""
+
+    def __init__(self, stepper, ewald_gridsize=64):
+        self.stepper = stepper
+        self.cfg = stepper.cfg
+        stepper.ewald_gridsize = int(ewald_gridsize)
+
+    def step(self, pos, mom, dt_kick, dt_drift):
+        return self.stepper.step(pos, mom, dt_kick, dt_drift, periodic_pp="ewald")
+
+
 def edges_through(a_begin, output_times, dlna_max=0.025):
     """Step edges from a_begin that hit every output time exactly; returns (edges, output indices)."""
     outs = sorted(float(a) for a in output_times if a > a_begin)
@@ -199,6 +212,8 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
     eng = engine or default_engine()
     cfg.a = 1.0
     stepper = F.ForceStepper(cfg, eng)
+    if cfg.method == "pp":
+        stepper = PeriodicPP(stepper)
     lpt = int((vals.get("realization_options") or {}).get("LPT", 1))
     pos, mom = zeldovich_ics(cosmo, cfg.boxsize, n, cfg.a_begin, cfg.mass, A_s=float(prim.get("A_s", 2.1e-9)),
                              n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt)

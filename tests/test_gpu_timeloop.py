@@ -141,3 +141,33 @@ def test_param_driven_run_grows_linearly_at_low_k_and_writes_snapshots(tmp_path)
     # against the linear spectrum itself: band-averaged over the low bins (few modes per bin)
     lin = c.linear_power(k[low])
     assert abs(np.mean(p_one[low] / lin) - 1) < 0.35
+
+
+def test_periodic_pp_steps_use_the_ewald_force():
+    """`pp` in the comoving loop is periodic: timeloop.PeriodicPP steps with nearest image + Ewald
+    table; three steps against the same loop on the float64 restatement (table of 16 intervals)."""
+    from nbody_b200 import force as F
+    from nbody_b200 import timeloop
+    from nbody_b200.cosmo import Cosmology, scale_factor_edges
+    from nbody_b200.engine import default_engine
+    from oracle import force as oforce
+    c = Cosmology()
+    L, n, a0 = 400.0, 6, 0.05
+    cfg = _physical_cfg("pp", n, 0, L, c)
+    pos0, mom0, _psi, _q, _ = numpy_zeldovich(c, L, n, a0, cfg.mass, seed=4)
+    table = oforce.ewald_table(L, 16)
+
+    class OracleEwald:
+        def __init__(self):
+            self.cfg = cfg
+
+        def step(self, pos, mom, dt_kick, dt_drift):
+            acc = oforce.pp_accel_ewald(pos, L, table, G=cfg.G, mass=cfg.mass, eps=cfg.eps)
+            return oforce.kick_drift(pos, mom, acc, L, mass=cfg.mass, a=1.0, dt_kick=dt_kick, dt_drift=dt_drift)
+    edges = scale_factor_edges(a0, a0 * math.exp(0.15), 0.05)
+    p_ref, m_ref = timeloop.evolve(OracleEwald(), c, pos0, mom0, edges)
+    eng = default_engine()
+    st = timeloop.PeriodicPP(F.ForceStepper(cfg, eng), ewald_gridsize=16)
+    p, m = timeloop.evolve(st, c, eng.to_device(pos0), eng.to_device(mom0), edges)
+    assert _pdiff(p.cpu().numpy(), p_ref, L) <= 1e-7 * L
+    assert np.abs(m.cpu().numpy() - m_ref).max() <= 1e-4 * np.abs(m_ref).max()
