@@ -13,7 +13,10 @@ as a subprocess at TheFeedingPipeline/NeuNetværk_test.py:155-171 and SnapVsPK/U
   * the standard erfc / Gaussian force split and Plummer softening.
 The CUDA kernels are checked against this file; this file is checked against analytic
 properties in tests/test_force_oracle.py (Newton's third law, 1/r² at long range,
-PM + short-range = softened Newton, interlacing removes odd aliases).
+PM + short-range = softened Newton, interlacing removes odd aliases).  The periodic PP force
+(`ewald_force`, `ewald_table`, `pp_accel_ewald`: Ewald summation after Hernquist, Bouchet & Suto
+1991, the method CONCEPT documents for its PP gravity) is checked in tests/test_ewald_cpu.py
+(independence of the splitting parameter, periodicity, symmetry zeros, small-separation limit).
 """
 from __future__ import annotations
 
