@@ -43,6 +43,9 @@ WORKLOADS = {
     "pk": ("pk", 128, 256, 1000.0, "pk_particles_per_s", "particles/s"),
 }
 CPU_SAMPLE = {"p3m": (128, 256), "pm": (128, 256), "pp": (64, 0), "pk": (128, 256)}   # bounded CPU samples
+# --impl reference runs the CPU arm alone, so it can afford a sample 8x larger (1/8 of config 5 / the whole of
+# config 4's particle count at half its mesh): ~20 s per step on 16 host threads
+CPU_SAMPLE_REFERENCE = {"p3m": (256, 512), "pm": (256, 512), "pp": (64, 0), "pk": (128, 256)}
 FP32_LANES_PER_SM = 128
 
 
@@ -178,15 +181,24 @@ def cpu_step_once(workload, cfg, pos, mom, workers):
     return cpu_step.step(cfg, pos, mom, 1e-3, 1e-3, workers=workers)
 
 
-def cpu_measure(workload, steps=1, warmup=0):
+def host_threads():
+    """Threads this process may use: its CPU affinity mask, not an inherited OMP_NUM_THREADS (under
+    torch.distributed.run every rank is started with OMP_NUM_THREADS=1)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_measure(workload, steps=1, warmup=0, sample=None):
     from oracle import cport
-    n, N = CPU_SAMPLE[workload]
+    n, N = sample or CPU_SAMPLE[workload]
     L = WORKLOADS[workload][3]
     cfg = cpu_config(workload, n, N, L)
     pos = zeldovich_on_host(n, L, seed=11)
     mom = np.zeros_like(pos)
     cores = os.cpu_count() or 1
-    threads = cport.num_threads()
+    threads = cport.set_num_threads(host_threads())     # OpenMP loops; scipy.fft gets workers=threads
     for _ in range(warmup):
         cpu_step_once(workload, cfg, pos, mom, threads)
     t0 = time.perf_counter()
@@ -197,12 +209,16 @@ def cpu_measure(workload, steps=1, warmup=0):
     if workload == "pp":
         isub = min(n ** 3, 2048)
         value = isub * np3 / dt / 1e9
-        sample = f"{n}^3 particles, {isub} i-particles x all j per step (rate is size-independent)"
+        sample_txt = f"{n}^3 particles, {isub} i-particles x all j per step (rate is size-independent)"
     else:
         value = np3 / dt
-        sample = f"{n}^3 particles / {N}^3 mesh per step (1/{round((WORKLOADS[workload][1] / n) ** 3, 1)} of the workload)"
+        sample_txt = (f"{n}^3 particles / {N}^3 mesh per step (1/{round((WORKLOADS[workload][1] / n) ** 3, 1)} of the "
+                      "workload; particle-steps/s of the sample, i.e. extrapolated linearly in the particle count)")
+    sample = sample_txt
     return {"value": value, "unit": WORKLOADS[workload][5], "cores": threads, "host_cores": cores, "kind": "port",
-            "sample": sample, "seconds_per_sample_step": dt,
+            "sample": sample, "sample_particles": n ** 3, "sample_mesh": N, "seconds_per_sample_step": dt,
+            "extrapolated": workload != "pp" and n != WORKLOADS[workload][1],
+            "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
             "threads_note": "deposit loop serial like the reference's numba loop; gather, pair loops (OpenMP) and "
                             "scipy.fft use all threads"}
 
@@ -213,12 +229,19 @@ def run_reference(args):
         return
     wl = args.workload
     method, n, N, L, metric, unit = WORKLOADS[wl]
-    steps = max(1, min(args.steps, 3))
-    cb = cpu_measure(wl, steps=steps, warmup=min(args.warmup, 1))
+    steps = max(1, min(args.steps, 2))
+    warm = min(args.warmup, 1) if wl in ("pp", "pk") else 0      # a P3M sample step is ~20 s: no warm-up step
+    cb = cpu_measure(wl, steps=steps, warmup=warm, sample=CPU_SAMPLE_REFERENCE[wl])
+    cfgd = workload_config(wl, n, N, L)
+    # what was actually timed: the sample's particle count and mesh, with the full workload beside it
+    cfgd.update(particles=cb["sample_particles"], mesh=cb["sample_mesh"], extrapolated=cb["extrapolated"],
+                full_workload={"particles": n ** 3, "mesh": N},
+                note="CPU arm = the repo's float64 C/OpenMP + scipy.fft restatement (the reference has no force "
+                     "solver of its own: CONCEPT is external), timed on a bounded sample of the workload")
     line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": unit, "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": cb["seconds_per_sample_step"] * 1e3,
+            "steps": steps, "warmup": warm, "ms_per_step": cb["seconds_per_sample_step"] * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": workload_config(wl, n, N, L),
+            "data": "synthetic", "config": cfgd,
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -265,7 +288,13 @@ def run_ours(args):
         N = args.mesh
     eng = Engine(local)
     hbm_peak, peak_src, sm_max_mhz = peaks()
-    fp32_peak_tf = 2.0 * FP32_LANES_PER_SM * eng_num_sms(torch, local) * sm_max_mhz * 1e6 / 1e12
+    fp32_nominal_tf = 2.0 * FP32_LANES_PER_SM * eng_num_sms(torch, local) * sm_max_mhz * 1e6 / 1e12
+    # measured denominators: pure-FMA microkernels of the library, scalar and packed
+    fp32_meas = {"ffma_tflops": eng.fp32_peak(packed=False), "ffma2_tflops": eng.fp32_peak(packed=True),
+                 "nominal_tflops": fp32_nominal_tf,
+                 "how": "nb_fp32_peak: 64 independent FMAs per thread and iteration, 2 x 1024 threads per SM, best of 5 "
+                        "launches, CUDA events; nominal = 2 x 128 lanes x SMs x clocks.max.sm"}
+    fp32_peak_tf = max(fp32_meas["ffma_tflops"], fp32_meas["ffma2_tflops"])
     np_total = n ** 3
     dt_kick, dt_drift = 1e-3, 1e-3
     cfg = ForceConfig(method=method if method != "pk" else "pm", npart=np_total, boxsize=L, gridsize=N,
@@ -375,6 +404,22 @@ def run_ours(args):
     t_end = ev()
     barrier()
     launches = eng.launch_count() - launches0
+    invariants = None
+    if method != "pk":
+        # state after W + K steps from the same initial set at every N: conserved / partition-independent
+        # quantities, so the SCALE lines carry a correctness signal
+        p_, m_ = state["pos"], state["mom"]
+        inv = torch.cat([torch.tensor([float(p_.shape[0])], device=eng.device, dtype=torch.float64),
+                         m_.sum(0), m_.abs().sum(0), p_.sum(0), (m_ * m_).sum().reshape(1)])
+        if world > 1:
+            dist.all_reduce(inv)
+        inv = inv.cpu().tolist()
+        invariants = {"n_particles_total": int(round(inv[0])), "n_particles_expected": int(np_total),
+                      "mom_sum": inv[1:4], "mom_abs_sum": inv[4:7], "pos_sum": inv[7:10], "mom_sq_sum": inv[10],
+                      "after_steps": int(args.warmup + args.steps),
+                      "note": "identical initial set and step count at every N: n_particles_total is conserved, "
+                              "|mom_sum| << mom_abs_sum (Newton's third law), pos_sum / mom_sq_sum agree across N to "
+                              "the float32 force tolerance"}
     if world == 1 and method != "pk":
         # phase pass (not part of `value`): the same kernels one after the other on one stream,
         # CUDA events around each, for phase_ms and the per-kernel rooflines
@@ -415,6 +460,8 @@ def run_ours(args):
                                                         "gather + kick + drift tail)" if method == "p3m" else ""))
     if phase_by_rank is not None:
         line["phase_ms_by_rank"] = phase_by_rank
+    if invariants is not None:
+        line["invariants"] = invariants
     line["config"]["parallelism"] = ("single GPU" if world == 1 else
                                      f"{world} ranks, i-sharded + all-gather of j" if method == "pp" else
                                      f"{world} x-slabs: slab FFT all-to-all, ghost planes, halo particles")
@@ -422,12 +469,23 @@ def run_ours(args):
     # ---- rooflines ------------------------------------------------------------------------
     line.update(rooflines(eng, method, cfg, state["pos"], phase_ms, n, N, L, hbm_peak, peak_src, fp32_peak_tf, world,
                           stepper, torch))
+    line["fp32_peak"] = fp32_meas
     # ---- end to end through host buffers ----------------------------------------------------
     if world == 1:
         line["e2e"] = e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work, unit, L, N,
                                   np_total)
     else:
         line["e2e"] = e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier)
+    if wl == "p3m" and not args.no_secondary and not args.n:
+        # BASELINE.json's metric names PM particle-steps/s and PP Ginteractions/s too: short runs of configs 4
+        # and 3 after the headline workload, so that they are driver-observed
+        del pos, mom, stepper
+        state.clear()
+        eng.release_scratch()
+        torch.cuda.empty_cache()
+        line["secondary"] = {w: secondary_measure(torch, dist, eng, w, rank, world, fp32_peak_tf, hbm_peak, barrier)
+                             for w in ("pm", "pp")}
+        pos = mom = None
     if rank == 0:
         line["clocks"] = clocks
         if world == 1 and not args.no_cpu:
@@ -437,6 +495,62 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def secondary_measure(torch, dist, eng, wl, rank, world, fp32_peak_tf, hbm_peak, barrier, steps=3, warmup=1):
+    """Device-timed product steps of another BASELINE workload (inputs resident, CUDA events, max over
+    ranks): config 4 (PM, 256^3 / 512^3) and config 3 (PP, 128^3)."""
+    from nbody_b200.force import ForceStepper
+    from nbody_b200.params import ForceConfig
+    method, n, N, L, metric, unit = WORKLOADS[wl]
+    try:
+        cfg = ForceConfig(method=method, npart=n ** 3, boxsize=L, gridsize=N, interlace=(True, True),
+                          deconvolve=(True, True))
+        pos = zeldovich_on_device(eng, n, L, seed=20250611)
+        if world > 1:
+            from nbody_b200.dist import DistForceStepper, shard_particles
+            shard = shard_particles(pos, method, L, rank, world, N)
+            del pos
+            st = {"pos": shard, "mom": torch.zeros_like(shard)}
+            stepper = DistForceStepper(cfg, eng, rank, world)
+
+            def step():
+                st["pos"], st["mom"] = stepper.step(st["pos"], st["mom"], 1e-3, 1e-3, n_total=n ** 3)
+        else:
+            st = {"pos": pos, "mom": torch.zeros_like(pos)}
+            stepper = ForceStepper(cfg, eng)
+
+            def step():
+                stepper.step(st["pos"], st["mom"], 1e-3, 1e-3)
+        for _ in range(warmup):
+            step()
+        barrier()
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            step()
+        b.record()
+        barrier()
+        t = torch.tensor([a.elapsed_time(b) / steps], device=eng.device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        work = float(n ** 3) ** 2 / 1e9 if method == "pp" else float(n ** 3)
+        out = {"metric": metric, "value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
+               "warmup": warmup, "n_gpus": world, "config": workload_config(wl, n, N, L),
+               "timing": "whole product step (ForceStepper.step / DistForceStepper.step), inputs resident"}
+        if method == "pp":
+            # the step is the pair kernel plus a 2 M-particle pack and kick/drift (< 0.1 %): step-level fraction
+            ach = float(n ** 3) ** 2 * PP_FLOP / (ms * 1e-3) / 1e12
+            out["roofline"] = {"bound": "fp32", "achieved": ach, "peak": fp32_peak_tf * world, "unit": "TFLOP/s",
+                               "frac": ach / (fp32_peak_tf * world), "flop_per_interaction": PP_FLOP,
+                               "peak_source": "measured FMA microkernel x n_gpus"}
+        del st, stepper
+        eng.release_scratch()
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:      # a secondary block must never take the headline line down
+        return {"metric": metric, "error": f"{type(e).__name__}: {e}"}
 
 
 def eng_num_sms(torch, dev):
@@ -493,7 +607,7 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
         fp = {"kernel": "pp_accel (K4, FFMA2 j-tile)", "bound": "fp32", "ms": phase_ms["pp_accel"], "achieved": ach,
               "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
               "flop_per_interaction": PP_FLOP, "interactions_per_launch": inter,
-              "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
+              "peak_source": "measured FMA microkernel (max of FFMA / FFMA2, see fp32_peak)"}
     if method == "p3m" and "p3m_short" in phase_ms:
         if world == 1:
             srt = eng.cell_sort(pos, L, stepper.ncs, mass=1.0)
@@ -509,7 +623,7 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
               "achieved": ach, "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": ach / fp32_peak_tf, "traffic": None,
               "flop_per_inrange_pair": P3M_FLOP, "inrange_pairs": inr, "candidate_pairs": cand,
               "candidate_pairs_per_s": cand / t,
-              "peak_source": "2 x 128 FP32 lanes x SMs x clocks.max.sm (not in MEASURED_PEAKS.json)"}
+              "peak_source": "measured FMA microkernel (max of FFMA / FFMA2, see fp32_peak)"}
     allk = hbm + ([fp] if fp else [])
     # DRAM traffic per launch from the committed ncu --set full captures (profiles/ncu_traffic.json);
     # it cannot be measured live, so it is only filled in for the exact size that was captured
@@ -639,6 +753,7 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="override particles per side (development only)")
     ap.add_argument("--mesh", type=int, default=0, help="override mesh size (development only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development only)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the PM / PP secondary blocks of the default line")
     ap.add_argument("--subphases", action="store_true", help="finer CUDA-event marks inside the slab FFT (development only)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 5
+#define NB_ABI_VERSION 6
 
 #define NB_OK 0
 #define NB_EINVAL (-1)  /* bad argument */
@@ -64,6 +64,10 @@ int64_t nb_launch_count(nb_ctx* ctx);
 #define NB_PH_COUNT 6
 int nb_profile_enable(nb_ctx* ctx, int on);
 int nb_profile_read(nb_ctx* ctx, double* ms_sum_host, int64_t* count_host, int nphases);
+/* Measured FP32 roofline denominator for the pair kernels K4/K5 ("FP32 peak computed, not
+ * measured"): a pure-FMA microkernel, packed = 0 scalar FFMA, 1 packed FFMA2 (fma.rn.f32x2).  Best of
+ * `reps` launches of `iters` x 64 FMAs per thread on 2 x 1024 threads per SM, in TFLOP/s (2 flop per lane). */
+int nb_fp32_peak(nb_ctx* ctx, int packed, int iters, int reps, double* tflops_host, void* stream);
 
 /* ---- K1  CIC mass deposit -------------------------------------------------------------
  * Replaces cic_density(positions, boxsize, N)   FraP_kTilDelta.py:93-123,
@@ -126,6 +130,19 @@ int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec, const dou
                       double thresh_last, double thresh_hi, int n_edges, int window_power,
                       int clip_mode, double clip_val, double norm, int closed_last,
                       int64_t* counts, double* sums, void* stream);
+
+/* CONCEPT-style estimator front end (options `powerspec_options['interlace']`,
+ * `['deconvolve']` of SnapVsPK/Uncertain.param:29-62; outputs to match: PPPMP3M/{PP,PM,P3M}/powerspec/
+ * powerspec_a=1.00, SnapVsPK/powerspec/powerspec_a={0.17,1.00}).  Same as nb_power_spectrum with a
+ * second real grid `delta_shifted` = the CIC deposit on the mesh shifted by half a cell in x, y, z
+ * (nb_cic_deposit with shift = cell/2): both are transformed and combined as
+ * 0.5 (d1_k + d2_k e^{+i k.s}) before the |.|^2 / W^window_power binning (window_power = 2 is the
+ * CIC deconvolution of the power).  The caller passes bin thresholds in k^2 (any increasing edges). */
+int nb_power_spectrum_interlaced(nb_ctx* ctx, const void* delta, const void* delta_shifted, int N, int prec,
+                                 const double* k2_tab, const double* sinc_tab, const double* thresh,
+                                 double thresh_first, double thresh_last, double thresh_hi, int n_edges,
+                                 int window_power, int clip_mode, double clip_val, double norm,
+                                 int closed_last, int64_t* counts, double* sums, void* stream);
 
 /* ---- K7  Gaussian random field from P(k) ------------------------------------------------
  * nb_hermitian_R replaces createR's symmetrisation loop (Cosmo data create (new).py:35-45;

@@ -25,12 +25,15 @@ PROTOTYPES = {
     "nb_launch_count": (c_i64, [c_vp]),
     "nb_profile_enable": (c_i32, [c_vp, c_i32]),
     "nb_profile_read": (c_i32, [c_vp, c_vp, c_vp, c_i32]),
+    "nb_fp32_peak": (c_i32, [c_vp, c_i32, c_i32, c_i32, C.POINTER(c_f64), c_vp]),
     "nb_cic_deposit": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i32, c_f64, c_i32, c_vp, c_vp]),
     "nb_grid_sum": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp]),
     "nb_grid_affine": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_f64, c_vp, c_f64, c_f64, c_f64, c_vp]),
     "nb_deconvolve_cic": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_i32, c_vp]),
     "nb_power_spectrum": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_f64, c_f64, c_f64, c_i32,
                                   c_i32, c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),
+    "nb_power_spectrum_interlaced": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_f64, c_f64, c_f64,
+                                             c_i32, c_i32, c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),
     "nb_hermitian_R": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp]),
     "nb_grf_synthesize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_f64, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "nb_cic_gather": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_vp, c_vp]),
@@ -99,7 +102,7 @@ def load():
     return lib
 
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 def check(rc: int, what: str = ""):

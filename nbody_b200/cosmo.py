@@ -107,15 +107,63 @@ class Cosmology:
         C0 = 14.2 + 731.0 / (1.0 + 62.5 * q)
         return L0 / (L0 + C0 * q * q)
 
-    def linear_power(self, k, A_s=2.1e-9, n_s=0.9649, a=1.0):
+    def transfer_eh98(self, k):
+        """Eisenstein & Hu (1998) transfer function WITH baryons (acoustic oscillations and Silk
+        damping; their eqs. 2-24, the `TFfit_onek` formulae), k in 1/Mpc.  Against the `P_linear`
+        column of the reference's powerspec files (CLASS, PPPMP3M/P3M/powerspec/powerspec_a=1.00:11-26)
+        the resulting spectrum is within 3 % per bin (tests/test_concept_powerspec.py)."""
+        k = np.asarray(k, dtype=np.float64)
+        h = self.h
+        omhh, obhh = self.Omega_m * h * h, self.Omega_b * h * h
+        fb = obhh / omhh
+        th = T_CMB / 2.7
+        z_eq = 2.50e4 * omhh / th ** 4
+        k_eq = 0.0746 * omhh / th ** 2
+        b1 = 0.313 * omhh ** -0.419 * (1.0 + 0.607 * omhh ** 0.674)
+        b2 = 0.238 * omhh ** 0.223
+        z_d = 1291.0 * omhh ** 0.251 / (1.0 + 0.659 * omhh ** 0.828) * (1.0 + b1 * obhh ** b2)
+        R_d = 31.5 * obhh / th ** 4 * (1000.0 / (1.0 + z_d))
+        R_eq = 31.5 * obhh / th ** 4 * (1000.0 / z_eq)
+        s = 2.0 / 3.0 / k_eq * math.sqrt(6.0 / R_eq) * math.log(
+            (math.sqrt(1.0 + R_d) + math.sqrt(R_d + R_eq)) / (1.0 + math.sqrt(R_eq)))
+        k_silk = 1.6 * obhh ** 0.52 * omhh ** 0.73 * (1.0 + (10.4 * omhh) ** -0.95)
+        a1 = (46.9 * omhh) ** 0.670 * (1.0 + (32.1 * omhh) ** -0.532)
+        a2 = (12.0 * omhh) ** 0.424 * (1.0 + (45.0 * omhh) ** -0.582)
+        alpha_c = a1 ** -fb * a2 ** -(fb ** 3)
+        bb1 = 0.944 / (1.0 + (458.0 * omhh) ** -0.708)
+        bb2 = (0.395 * omhh) ** -0.0266
+        beta_c = 1.0 / (1.0 + bb1 * ((1.0 - fb) ** bb2 - 1.0))
+        y = z_eq / (1.0 + z_d)
+        G = y * (-6.0 * math.sqrt(1.0 + y) + (2.0 + 3.0 * y) * math.log(
+            (math.sqrt(1.0 + y) + 1.0) / (math.sqrt(1.0 + y) - 1.0)))
+        alpha_b = 2.07 * k_eq * s * (1.0 + R_d) ** -0.75 * G
+        beta_node = 8.41 * omhh ** 0.435
+        beta_b = 0.5 + fb + (3.0 - 2.0 * fb) * math.sqrt((17.2 * omhh) ** 2 + 1.0)
+        q = k / (13.41 * k_eq)
+        xx = k * s
+        ln_b = np.log(math.e + 1.8 * beta_c * q)
+        ln_nb = np.log(math.e + 1.8 * q)
+        C_na = 14.2 + 386.0 / (1.0 + 69.9 * q ** 1.08)
+        C_a = 14.2 / alpha_c + 386.0 / (1.0 + 69.9 * q ** 1.08)
+        f = 1.0 / (1.0 + (xx / 5.4) ** 4)
+        T_c = f * ln_b / (ln_b + C_na * q * q) + (1.0 - f) * ln_b / (ln_b + C_a * q * q)
+        s_t = s * (1.0 + (beta_node / xx) ** 3) ** (-1.0 / 3.0)
+        T0 = ln_nb / (ln_nb + C_na * q * q)
+        T_b = np.sinc(k * s_t / math.pi) * (T0 / (1.0 + (xx / 5.2) ** 2)
+                                            + alpha_b / (1.0 + (beta_b / xx) ** 3) * np.exp(-(k / k_silk) ** 1.4))
+        return fb * T_b + (1.0 - fb) * T_c
+
+    def linear_power(self, k, A_s=2.1e-9, n_s=0.9649, a=1.0, wiggles=True):
         """P(k, a) in Mpc³ (convention P = |δ_k|² / V): primordial curvature spectrum
-        2π² A_s k⁻³ (k/k_pivot)^(n_s−1) times [(2/5) (k c/H0)² T(k) D₊(a) / Ωm]²."""
+        2π² A_s k⁻³ (k/k_pivot)^(n_s−1) times [(2/5) (k c/H0)² T(k) D₊(a) / Ωm]².  T is the
+        Eisenstein-Hu form with baryons (wiggles=True) or their zero-baryon fit."""
         k = np.asarray(k, dtype=np.float64)
         out = np.zeros_like(k)
         ok = k > 0
         kk = k[ok]
         prim = 2.0 * math.pi ** 2 * A_s / kk ** 3 * (kk / K_PIVOT) ** (n_s - 1.0)
-        amp = 0.4 * (kk * C_LIGHT / self.H0) ** 2 * self.transfer(kk) * self.growth(a) / self.Omega_m
+        tk = self.transfer_eh98(kk) if wiggles else self.transfer(kk)
+        amp = 0.4 * (kk * C_LIGHT / self.H0) ** 2 * tk * self.growth(a) / self.Omega_m
         out[ok] = prim * amp * amp
         return out
 

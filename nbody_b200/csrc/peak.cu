@@ -1,0 +1,79 @@
+// FP32 roofline denominators measured on the device the bench runs on: dependent-chain-free
+// FFMA and packed FFMA2 (fma.rn.f32x2, the form the pair kernels K4/K5 issue on sm_100a)
+// microkernels.  8 independent accumulators (16 for the packed form) per thread, 1024 threads per
+// CTA, 2 CTAs per SM -> every SMSP has 16 warps of pure FMA issue.  Timed with CUDA events
+// on the caller's stream; 2 flop per FMA lane.
+#include "common.cuh"
+
+template <int PACKED>
+__global__ void __launch_bounds__(1024, 2)
+fp32_peak_kernel(float* __restrict__ out, int iters, float a, float b) {
+  const float t = (float)threadIdx.x * 1e-6f;
+  if (PACKED) {
+    unsigned long long x[8], aa, bb;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(aa) : "f"(a), "f"(a));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(bb) : "f"(b), "f"(b));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) asm("mov.b64 %0, {%1, %2};" : "=l"(x[i]) : "f"(t + i), "f"(t - i));
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x[i]) : "l"(aa), "l"(bb));
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float lo, hi;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(x[i]));
+      s += lo + hi;
+    }
+    if (s == 12345.678f) out[0] = s;
+  } else {
+    float x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = t + i;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(x[i]) : "f"(a), "f"(b));
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[i];
+    if (s == 12345.678f) out[0] = s;
+  }
+}
+
+// packed = 0: scalar FFMA, 1: FFMA2.  Returns the best of `reps` launches in TFLOP/s (host double).
+extern "C" int nb_fp32_peak(nb_ctx* ctx, int packed, int iters, int reps, double* tflops_host, void* stream) {
+  NB_REQUIRE(ctx && tflops_host, "NULL argument");
+  NB_REQUIRE(iters >= 1 && reps >= 1 && reps <= 100, "bad iters / reps");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  void* out = nullptr;
+  int rc = nb_scratch(ctx, NB_SCR_MISC0, 256, &out);
+  if (rc) return rc;
+  const int nblk = ctx->num_sms * 2;
+  cudaEvent_t e0, e1;
+  NB_CHECK_CUDA(cudaEventCreate(&e0));
+  NB_CHECK_CUDA(cudaEventCreate(&e1));
+  double best = 0.0;
+  for (int r = 0; r <= reps; ++r) {     // launch 0 is the warm-up
+    NB_CHECK_CUDA(cudaEventRecord(e0, st));
+    if (packed) fp32_peak_kernel<1><<<nblk, 1024, 0, st>>>((float*)out, iters, 0.999f, 1e-3f);
+    else fp32_peak_kernel<0><<<nblk, 1024, 0, st>>>((float*)out, iters, 0.999f, 1e-3f);
+    NB_CHECK_CUDA(cudaEventRecord(e1, st));
+    NB_CHECK_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    NB_CHECK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    NB_LAUNCHED(ctx);
+    const double fl = 2.0 * (packed ? 2.0 : 1.0) * 64.0 * (double)iters * 1024.0 * (double)nblk;
+    if (r > 0 && ms > 0.f && fl / (ms * 1e-3) / 1e12 > best) best = fl / (ms * 1e-3) / 1e12;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *tflops_host = best;
+  return NB_OK;
+}

@@ -555,11 +555,63 @@ int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, in
   return NB_OK;
 }
 
-extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec, const double* k2_tab,
-                                 const double* sinc_tab, const double* thresh, double thresh_first,
-                                 double thresh_last, double thresh_hi, int n_edges, int window_power,
-                                 int clip_mode, double clip_val, double norm, int closed_last,
-                                 int64_t* counts, double* sums, void* stream) {
+// Upstream interlacing for the estimator (CONCEPT `powerspec_options['interlace']`,
+// SnapVsPK/Uncertain.param:43-45): s1 <- 0.5 (s1 + s2 · e^{+i k·s}), s = half a cell along x, y and z,
+// s2 the spectrum of the deposit on the half-cell-shifted mesh.  Same phase convention and Nyquist
+// treatment (Hermitian part of e^{±iπ/2} = 0) as the force path's K2 (kspace.cu).
+template <typename C2, typename T>
+__global__ void __launch_bounds__(256)
+pk_interlace_combine_kernel(C2* __restrict__ s1, const C2* __restrict__ s2, int N) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* s_pc = reinterpret_cast<T*>(smem_raw);
+  T* s_ps = s_pc + N;
+  const int nyq = (N % 2 == 0) ? N / 2 : -1;
+  for (int m = threadIdx.x; m < N; m += blockDim.x) {
+    const int ms = (m <= N / 2 && m != nyq) ? m : m - N;
+    double sn, cs;
+    sincospi((double)ms / (double)N, &sn, &cs);
+    s_pc[m] = (m == nyq) ? (T)0 : (T)cs;
+    s_ps[m] = (m == nyq) ? (T)0 : (T)sn;
+  }
+  __syncthreads();
+  const int nzh = N / 2 + 1;
+  const int64_t nrows = (int64_t)N * N;
+  const int warps = blockDim.x >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t row = (int64_t)blockIdx.x * warps + warp; row < nrows; row += (int64_t)gridDim.x * warps) {
+    const int j = (int)(row % N), i = (int)(row / N);
+    const T pcxy = s_pc[i] * s_pc[j] - s_ps[i] * s_ps[j];
+    const T psxy = s_pc[i] * s_ps[j] + s_ps[i] * s_pc[j];
+    const int64_t base = row * nzh;
+    for (int kz = lane; kz < nzh; kz += 32) {
+      const T pc = pcxy * s_pc[kz] - psxy * s_ps[kz];
+      const T ps = pcxy * s_ps[kz] + psxy * s_pc[kz];
+      C2 r = s1[base + kz];
+      const C2 q = s2[base + kz];
+      r.x = (T)0.5 * (r.x + q.x * pc - q.y * ps);
+      r.y = (T)0.5 * (r.y + q.x * ps + q.y * pc);
+      s1[base + kz] = r;
+    }
+  }
+}
+
+static int pk_forward(nb_ctx* ctx, const void* delta, int N, int prec, void* spec, cudaStream_t st) {
+  cufftHandle fwd;
+  int rc;
+  NbPhase phf(ctx, NB_PH_FFT_FWD, st);
+  if (prec == NB_F64) {
+    if ((rc = nb_plan3d(ctx, N, CUFFT_D2Z, st, &fwd))) return rc;
+    NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)const_cast<void*>(delta), (cufftDoubleComplex*)spec));
+  } else {
+    if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
+    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)const_cast<void*>(delta), (cufftComplex*)spec));
+  }
+  return NB_OK;
+}
+
+static int pk_spectrum_impl(nb_ctx* ctx, const void* delta, const void* delta2, int N, int prec, const double* k2_tab,
+                            const double* sinc_tab, const double* thresh, double thresh_first, double thresh_last,
+                            double thresh_hi, int n_edges, int window_power, int clip_mode, double clip_val,
+                            double norm, int closed_last, int64_t* counts, double* sums, void* stream) {
   NB_REQUIRE(ctx && delta && k2_tab && sinc_tab && thresh && counts && sums, "NULL argument");
   NB_REQUIRE(N >= 2 && n_edges >= 2, "bad N / n_edges");
   NB_REQUIRE(prec == NB_F32 || prec == NB_F64, "bad prec");
@@ -567,19 +619,22 @@ extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
   const int64_t nspec = (int64_t)N * N * (N / 2 + 1);
-  void* spec = nullptr;
-  int rc = nb_scratch(ctx, NB_SCR_SPEC0, (size_t)nspec * (prec == NB_F64 ? 16 : 8), &spec);
+  const size_t cbytes = (size_t)nspec * (prec == NB_F64 ? 16 : 8);
+  void *spec = nullptr, *spec2 = nullptr;
+  int rc = nb_scratch(ctx, NB_SCR_SPEC0, cbytes, &spec);
   if (rc) return rc;
-  cufftHandle fwd;
-  {
-    NbPhase phf(ctx, NB_PH_FFT_FWD, st);
-    if (prec == NB_F64) {
-      if ((rc = nb_plan3d(ctx, N, CUFFT_D2Z, st, &fwd))) return rc;
-      NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)const_cast<void*>(delta), (cufftDoubleComplex*)spec));
-    } else {
-      if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
-      NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)const_cast<void*>(delta), (cufftComplex*)spec));
-    }
+  if ((rc = pk_forward(ctx, delta, N, prec, spec, st))) return rc;
+  if (delta2) {
+    if ((rc = nb_scratch(ctx, NB_SCR_SPEC1, cbytes, &spec2))) return rc;
+    if ((rc = pk_forward(ctx, delta2, N, prec, spec2, st))) return rc;
+    int nblk = ctx->num_sms * 4;
+    const int64_t need = ((int64_t)N * N + 7) / 8;
+    if (nblk > need) nblk = (int)need;
+    if (prec == NB_F64)
+      pk_interlace_combine_kernel<double2, double><<<nblk, 256, 2 * sizeof(double) * N, st>>>((double2*)spec, (const double2*)spec2, N);
+    else
+      pk_interlace_combine_kernel<float2, float><<<nblk, 256, 2 * sizeof(float) * N, st>>>((float2*)spec, (const float2*)spec2, N);
+    NB_LAUNCHED(ctx);
   }
   NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * (n_edges - 1), st));
   NB_CHECK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * (n_edges - 1), st));
@@ -587,6 +642,28 @@ extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec
   NbPhase ph(ctx, NB_PH_PK_BIN, st);
   return nb_pk_bin_spectrum(ctx, spec, N, 0, N, prec, k2_tab, sinc_tab, thresh, thresh_hi, n_edges, window_power,
                             clip_mode, clip_val, norm, closed_last, thresh_first, thresh_last, counts, sums, st);
+}
+
+extern "C" int nb_power_spectrum(nb_ctx* ctx, const void* delta, int N, int prec, const double* k2_tab,
+                                 const double* sinc_tab, const double* thresh, double thresh_first,
+                                 double thresh_last, double thresh_hi, int n_edges, int window_power,
+                                 int clip_mode, double clip_val, double norm, int closed_last,
+                                 int64_t* counts, double* sums, void* stream) {
+  return pk_spectrum_impl(ctx, delta, nullptr, N, prec, k2_tab, sinc_tab, thresh, thresh_first, thresh_last,
+                          thresh_hi, n_edges, window_power, clip_mode, clip_val, norm, closed_last, counts, sums,
+                          stream);
+}
+
+extern "C" int nb_power_spectrum_interlaced(nb_ctx* ctx, const void* delta, const void* delta_shifted, int N,
+                                            int prec, const double* k2_tab, const double* sinc_tab,
+                                            const double* thresh, double thresh_first, double thresh_last,
+                                            double thresh_hi, int n_edges, int window_power, int clip_mode,
+                                            double clip_val, double norm, int closed_last, int64_t* counts,
+                                            double* sums, void* stream) {
+  NB_REQUIRE(delta_shifted, "NULL argument");
+  return pk_spectrum_impl(ctx, delta, delta_shifted, N, prec, k2_tab, sinc_tab, thresh, thresh_first, thresh_last,
+                          thresh_hi, n_edges, window_power, clip_mode, clip_val, norm, closed_last, counts, sums,
+                          stream);
 }
 
 // Slab form: bins the y-slab [N][ny_local][N/2+1] (complex64) a rank holds after the slab-FFT

@@ -76,6 +76,13 @@ class Engine:
         _lib.check(self.lib.nb_profile_read(self.ctx, ms, cnt, n), "nb_profile_read")
         return {self.PHASES[i]: (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}
 
+    def fp32_peak(self, packed: bool = True, iters: int = 4096, reps: int = 5) -> float:
+        """Measured FP32 FMA throughput of this device in TFLOP/s (FFMA2 if packed, scalar FFMA else)."""
+        out = C.c_double(0.0)
+        _lib.check(self.lib.nb_fp32_peak(self.ctx, int(bool(packed)), int(iters), int(reps), C.byref(out),
+                                         self.stream), "nb_fp32_peak")
+        return float(out.value)
+
     def release_scratch(self):
         _lib.check(self.lib.nb_release_scratch(self.ctx), "nb_release_scratch")
 
@@ -203,6 +210,35 @@ class Engine:
                                               int(bool(closed_last)), _ptr(counts), _ptr(sums), self.stream),
                    "nb_power_spectrum")
         return edges, counts, sums
+
+    def power_spectrum_custom(self, delta: torch.Tensor, delta_shifted: torch.Tensor | None, L: float, N: int,
+                              thresholds, window_power: int = 0, norm: float = 1.0, kq_form: str = "inv_d"):
+        """|δ_k|²·norm/W^p summed over caller-defined shells: `thresholds` are increasing float64
+        values in k² (bin b holds thresholds[b] <= k² < thresholds[b+1]).  With `delta_shifted` (the
+        deposit on the half-cell-shifted mesh) the two spectra are interlaced first
+        (nb_power_spectrum_interlaced).  Returns (counts int64, sums float64) device tensors."""
+        for g in (delta, delta_shifted):
+            if g is not None and (g.shape != (N, N, N) or not g.is_contiguous() or g.dtype != delta.dtype):
+                raise ValueError("grids must be contiguous (N,N,N) tensors of one dtype")
+        thr = np.ascontiguousarray(thresholds, dtype=np.float64)
+        if thr.ndim != 1 or thr.size < 2 or not np.all(np.diff(thr) > 0) or thr[0] <= 0:
+            raise ValueError("thresholds must be positive and strictly increasing")
+        n_edges = int(thr.size)
+        thr_d = torch.from_numpy(thr).to(self.device)
+        k2 = self.table(("k2", N, float(L)), lambda: tables.k_vals(N, L) ** 2)
+        s = self.sinc_tab(N, L, kq_form)
+        counts = torch.empty(n_edges - 1, dtype=torch.int64, device=self.device)
+        sums = torch.empty(n_edges - 1, dtype=torch.float64, device=self.device)
+        args = (_ptr(k2), _ptr(s), _ptr(thr_d), float(thr[0]), float(thr[-1]), float(thr[-1]), n_edges,
+                int(window_power), 0, 0.0, float(norm), 0, _ptr(counts), _ptr(sums), self.stream)
+        if delta_shifted is None:
+            _lib.check(self.lib.nb_power_spectrum(self.ctx, _ptr(delta), int(N), _prec_of(delta), *args),
+                       "nb_power_spectrum")
+        else:
+            _lib.check(self.lib.nb_power_spectrum_interlaced(self.ctx, _ptr(delta), _ptr(delta_shifted), int(N),
+                                                             _prec_of(delta), *args),
+                       "nb_power_spectrum_interlaced")
+        return counts, sums
 
     # -- K7 ---------------------------------------------------------------------------
     def hermitian_R(self, c1: torch.Tensor, c2: torch.Tensor, guard: bool) -> torch.Tensor:

@@ -102,13 +102,21 @@ def edges_through(a_begin, output_times, dlna_max=0.025):
     return np.concatenate(edges), idx
 
 
-def linear_pk_grid(cosmo: Cosmology, L, n, A_s, n_s, a=1.0):
+def linear_pk_grid(cosmo: Cosmology, L, n, A_s, n_s, a=1.0, linear_power=None):
     """P(k, a) on the (n,n,n) FFT grid in the reference's GRF convention (the `fac` of
     `Cosmo data create (new).py:130-137` carries a factor 2π: |δ_k|² = P·2π·N⁶/V), so that the
-    realisation's spectrum in the usual convention |δ_k|² V / N⁶ is the linear P(k)."""
+    realisation's spectrum in the usual convention |δ_k|² V / N⁶ is the linear P(k).
+    `linear_power`: callable k -> P(k, a=1) replacing the closed-form spectrum of cosmo.py (the
+    reference passes CLASS output here; the full-run pin passes a table built from the
+    `P_linear` column of the reference's powerspec files)."""
     kv = tables.k_vals(n, L)
     k2 = kv[:, None, None] ** 2 + kv[None, :, None] ** 2 + kv[None, None, :] ** 2
-    pk = cosmo.linear_power(np.sqrt(k2), A_s=A_s, n_s=n_s, a=a) / (2.0 * math.pi)
+    if linear_power is not None:
+        pk = np.asarray(linear_power(np.sqrt(k2)), dtype=np.float64) / (2.0 * math.pi)
+        if a != 1.0:
+            pk = pk * (cosmo.growth(a) / cosmo.growth(1.0)) ** 2
+    else:
+        pk = cosmo.linear_power(np.sqrt(k2), A_s=A_s, n_s=n_s, a=a) / (2.0 * math.pi)
     pk[0, 0, 0] = 0.0
     return pk
 
@@ -146,7 +154,7 @@ def second_order_displacement(delta, L):
 
 
 def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649, seed=None, c1=None, c2=None,
-                  engine=None, lattice_offset=0.25, lpt=1):
+                  engine=None, lattice_offset=0.25, lpt=1, linear_power=None):
     """1LPT initial conditions on the device: (pos, mom) float64 (n³,3) tensors at a_begin.
     ψ(a=1) comes from nb_grf_synthesize on the particle lattice (grid nodes = lattice sites, no
     gather needed); x = q + D₊ψ (wrapped), mom = m a² H f D₊ ψ with D₊ normalised to 1 at a = 1.
@@ -162,7 +170,7 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
     from .engine import default_engine
     eng = engine or default_engine()
     n = int(n)
-    pk = linear_pk_grid(cosmo, L, n, A_s, n_s, a=1.0)
+    pk = linear_pk_grid(cosmo, L, n, A_s, n_s, a=1.0, linear_power=linear_power)
     c1, c2 = api._draws(n, c1, c2, seed)
     if lpt not in (1, 2):
         raise ValueError("lpt must be 1 or 2")

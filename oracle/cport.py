@@ -23,6 +23,7 @@ def lib():
             subprocess.check_call(["make", "-C", _HERE])
         L = C.CDLL(_PATH)
         L.oc_num_threads.restype = C.c_int
+        L.oc_set_num_threads.argtypes = [C.c_int]
         L.oc_cic_deposit.argtypes = [_dp, C.c_int64, C.c_double, C.c_int64, C.c_double, _dp]
         L.oc_cic_gather.argtypes = [_dp, C.c_int64, _dp, C.c_int64, C.c_double, C.c_double, _dp]
         L.oc_pp_accel.argtypes = [_dp, C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_double,
@@ -37,6 +38,12 @@ def lib():
 
 def num_threads():
     return int(lib().oc_num_threads())
+
+
+def set_num_threads(n):
+    """OpenMP threads of the C loops (overrides an inherited OMP_NUM_THREADS)."""
+    lib().oc_set_num_threads(int(n))
+    return num_threads()
 
 
 def cic_density(pos, boxsize, N, shift=0.0):

@@ -17,6 +17,12 @@ What is stored
                         CLASS_simualtor (Power_compare.py:279-331) and particle_assigment
                         (:336-418) with CLASS replaced by a surrogate P(k) (CLASS is absent)
   ref_window.npz        cic_window_ft both variants at N=8,16
+  concept_powerspec/    the five CONCEPT `powerspec_a=*` text files the reference ships
+                        (PPPMP3M/{PP,PM,P3M}/powerspec/powerspec_a=1.00, SnapVsPK/powerspec/
+                        powerspec_a={0.17,1.00}), copied byte for byte: the known answers of the
+                        CONCEPT-style estimator (modes / k columns) and of the full-run P(k) pin
+  snap_giant32_mom.npz  pos + mom + attributes of Different_Sizes/newrun2/3giant32p3m (32^3, L=1000,
+                        a=1) and mom of the 3giant32pm snapshot (momentum statistics of a full run)
 The CLASS substitution: the reference functions call `power_spectrum(...)` /
 `get_matter_power_spectrum(...)`; a stand-in with the same signature returning
 `surrogate_pk(k)` is injected into their namespace.  Everything else is reference code.
@@ -194,5 +200,34 @@ def main():
     print("golden vectors written to", OUT)
 
 
+def copy_concept_powerspec():
+    """The reference's five powerspec files -> tests/golden/concept_powerspec/ (byte copies) and the
+    momenta of the two 32^3 a=1 snapshots under Different_Sizes/newrun2."""
+    import shutil
+    dst = os.path.join(OUT, "concept_powerspec")
+    os.makedirs(dst, exist_ok=True)
+    R = ref_loader.REF_ROOT
+    for tag, rel in (("P3M_a=1.00", "PPPMP3M/P3M/powerspec/powerspec_a=1.00"),
+                     ("PM_a=1.00", "PPPMP3M/PM/powerspec/powerspec_a=1.00"),
+                     ("PP_a=1.00", "PPPMP3M/PP/powerspec/powerspec_a=1.00"),
+                     ("SnapVsPK_a=0.17", "SnapVsPK/powerspec/powerspec_a=0.17"),
+                     ("SnapVsPK_a=1.00", "SnapVsPK/powerspec/powerspec_a=1.00")):
+        shutil.copyfile(os.path.join(R, rel), os.path.join(dst, tag + ".txt"))
+    out = {}
+    for tag in ("pm", "p3m"):
+        f = os.path.join(R, "Different_Sizes", "newrun2", f"3giant32{tag}", "snapshots", "snapshot_a=1.00.hdf5")
+        out[f"mom_{tag}"] = snapshot.read_momenta(f)
+        if tag == "p3m":
+            out["pos_p3m"] = snapshot.read_positions(f)
+        at = snapshot.read_attrs(f)
+        for k in ("boxsize", "a", "H0"):
+            out[f"{k}_{tag}"] = float(at[k])
+    np.savez_compressed(os.path.join(OUT, "snap_giant32_mom.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "concept":
+        copy_concept_powerspec()
+    else:
+        main()
+        copy_concept_powerspec()

@@ -47,6 +47,16 @@ int oc_num_threads(void) {
 #endif
 }
 
+/* bench.py's CPU arm sets the thread count itself: under torch.distributed.run every rank inherits
+ * OMP_NUM_THREADS=1, which would time a single-threaded baseline. */
+void oc_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n >= 1) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 void oc_cic_deposit(const double* pos, int64_t np, double cell, int64_t N, double shift, double* grid) {
   for (int64_t p = 0; p < np; ++p) {
     const double x = pos[3 * p] + shift, y = pos[3 * p + 1] + shift, z = pos[3 * p + 2] + shift;
