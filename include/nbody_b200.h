@@ -97,6 +97,11 @@ int nb_grid_sum(nb_ctx* ctx, const void* grid, int64_t n, int prec, double* out_
  * sum / n without a host round trip). */
 int nb_grid_affine(nb_ctx* ctx, void* grid, int64_t n, int prec, double a, const double* a_dev,
                    double a_div, double b, double c, void* stream);
+/* max over i of |v_i|^2 for (n,3) float64 vectors (device scalar out; +inf if any component is NaN).  The
+ * sub-cycled time loop derives its number of short-range sub-steps from it (CONCEPT picks rungs from the
+ * short-range acceleration: the params_id0200_<A_s>.log files under TheFeedingPipeline/Datafolder4/
+ * Test_Data_concept, lines 42 and 55). */
+int nb_vec3_max_norm2(nb_ctx* ctx, const double* v, int64_t n, double* out_max, void* stream);
 
 /* ---- a3  CIC window deconvolution ------------------------------------------------------
  * Replaces deconvolve_cic(delta_grid, boxsize, ngrid)  FraP_kTilDelta.py:87-91 and

@@ -29,6 +29,7 @@ PROTOTYPES = {
     "nb_cic_deposit": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_i32, c_f64, c_i32, c_vp, c_vp]),
     "nb_grid_sum": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_vp, c_vp]),
     "nb_grid_affine": (c_i32, [c_vp, c_vp, c_i64, c_i32, c_f64, c_vp, c_f64, c_f64, c_f64, c_vp]),
+    "nb_vec3_max_norm2": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "nb_deconvolve_cic": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_i32, c_vp]),
     "nb_power_spectrum": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_f64, c_f64, c_f64, c_i32,
                                   c_i32, c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),

@@ -158,3 +158,44 @@ extern "C" int nb_deconvolve_cic(nb_ctx* ctx, void* grid, int N, int prec, const
   }
   return NB_OK;
 }
+
+// ------------------------------------------------------------------ max |a|² over (n,3) float64 vectors
+// Step-size criterion of the sub-cycled time loop (timeloop.evolve, SURVEY §8f row 1: CONCEPT assigns
+// particles to rungs by their short-range acceleration, log "Determining rung population" :42,55):
+// the largest squared acceleration of the set, one atomicMax per CTA on the bit pattern of a
+// non-negative double.
+__global__ void __launch_bounds__(256) vec3_max_norm2_kernel(const double* __restrict__ v, int64_t n,
+                                                              unsigned long long* out) {
+  double m = 0.0;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double x = v[3 * i], y = v[3 * i + 1], z = v[3 * i + 2];
+    const double s = x * x + y * y + z * z;
+    m = s > m ? s : m;            // NaN compares false: it is reported through the count below
+    if (!(s == s)) m = __longlong_as_double(0x7ff0000000000000LL);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const double t = __shfl_xor_sync(0xffffffffu, m, o);
+    m = t > m ? t : m;
+  }
+  __shared__ double part[8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) part[w] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < (int)(blockDim.x >> 5); ++k) m = part[k] > m ? part[k] : m;
+    atomicMax(out, (unsigned long long)__double_as_longlong(m));   // order-preserving for doubles >= 0
+  }
+}
+
+extern "C" int nb_vec3_max_norm2(nb_ctx* ctx, const double* v, int64_t n, double* out_max, void* stream) {
+  NB_REQUIRE(ctx && v && out_max && n >= 0, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  NB_CHECK_CUDA(cudaMemsetAsync(out_max, 0, sizeof(double), st));
+  if (n == 0) return NB_OK;
+  const int nblk = nb_grid_for(ctx, n, 256, 8);
+  vec3_max_norm2_kernel<<<nblk, 256, 0, st>>>(v, n, (unsigned long long*)out_max);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}

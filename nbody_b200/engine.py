@@ -141,6 +141,14 @@ class Engine:
                    "nb_grid_affine")
         return grid
 
+    def max_norm2(self, vec: torch.Tensor) -> torch.Tensor:
+        """max_i |v_i|² of an (n,3) float64 tensor as a device scalar (nb_vec3_max_norm2)."""
+        self._check_pos(vec)
+        out = torch.empty(1, dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.nb_vec3_max_norm2(self.ctx, _ptr(vec), vec.shape[0], _ptr(out), self.stream),
+                   "nb_vec3_max_norm2")
+        return out
+
     def compute_delta(self, grid: torch.Tensor) -> torch.Tensor:
         """density/density.mean() - 1 in place (FraP_kTilDelta.py:126-127)."""
         s = self.grid_sum(grid)

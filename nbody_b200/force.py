@@ -178,6 +178,43 @@ class ForceStepper:
             self.short_range(pos, acc, accumulate=True)
         return acc
 
+    # -- split interface of the sub-cycled time loop (timeloop.evolve_subcycled) ----------------
+    def accel_long(self, pos: torch.Tensor):
+        """Mesh (long-range) part of the acceleration, or None for a PP configuration."""
+        c = self.cfg
+        if c.method == "pp":
+            return None
+        f, fs = self.pm_mesh(pos)
+        acc = self._acc_buf(pos.shape[0])
+        self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, pos, None, acc, 1.0, 0.0, 0.0, c.boxsize)
+        return acc
+
+    def accel_short(self, pos: torch.Tensor):
+        """Pair (short-range) part: the P³M short range, the whole force for PP, None for PM."""
+        c = self.cfg
+        if c.method == "pm":
+            return None
+        n = pos.shape[0]
+        if self._acc_s is None or self._acc_s.shape[0] != n:
+            self._acc_s = torch.empty((n, 3), dtype=torch.float64, device=self.eng.device)
+        if c.method == "pp":
+            return self.pp(pos, self._acc_s, False)
+        return self.short_range(pos, self._acc_s, accumulate=False)
+
+    def kick(self, pos, mom, acc, k):
+        self.eng.kick_drift(pos, mom, acc, float(k), 0.0, self.cfg.boxsize)
+
+    def kick_drift(self, pos, mom, acc, k, d):
+        if acc is None:                      # drift only (PM between two mesh kicks)
+            z = getattr(self, "_zero_acc", None)
+            if z is None or z.shape[0] != pos.shape[0]:
+                z = self._zero_acc = torch.zeros((pos.shape[0], 3), dtype=torch.float64, device=self.eng.device)
+            acc, k = z, 0.0
+        self.eng.kick_drift(pos, mom, acc, float(k), float(d), self.cfg.boxsize)
+
+    def max_norm2(self, acc) -> float:
+        return float(self.eng.max_norm2(acc).item())
+
     def step(self, pos: torch.Tensor, mom: torch.Tensor, dt_kick: float, dt_drift: float,
              periodic_pp: bool = False):
         """One kick-drift step in place: mom += m·g·Δt_kick; pos += mom/(m a²)·Δt_drift; pos %= L."""

@@ -16,9 +16,12 @@ is built here is the part of such a run that sits directly on the hot path:
     outputs  synchronised (positions and momenta at the same a) copies at the requested times,
              optionally written as CONCEPT-layout snapshots (snapshot.write_snapshot)
 
-CONCEPT's adaptive Δt, rung sub-stepping and 2LPT are not restated: steps are uniform in ln a
-(cosmo.scale_factor_edges).  Results therefore compare with the reference's files at the level
-of P(k), not particle by particle.
+Base steps are uniform in ln a (cosmo.scale_factor_edges; CONCEPT's log shows Δln a ≈ 0.025 per step
+for a > 0.06, params_id0200_*.log:51-6617).  The short-range force of P³M and the PP force are
+sub-cycled inside a base step (`evolve_subcycled`: one rung for all particles, chosen per base step
+from the largest short-range acceleration) — without it the 64³ P³M run of the reference loses 5-15 %
+of its power at k > 0.1 / Mpc (tools/pin_concept.py).  Results compare with the reference's
+files at the level of P(k), not particle by particle.
 """
 from __future__ import annotations
 
@@ -75,6 +78,85 @@ def evolve(stepper, cosmo: Cosmology, pos, mom, a_edges, output_at=(), on_output
     return pos, mom
 
 
+def substep_count(cosmo: Cosmology, a0, a1, acc2_max, eps, eta=0.025, max_sub=32):
+    """Number of short-range sub-steps of the base step [a0, a1]: the smallest power of two n (the
+    rung 2^r of the most accelerated particle) with
+        Δt_base / n <= sqrt(2 η ε a³ / |g|_max),       Δt_base = ln(a1/a0) / H(a0),
+    where g is the comoving short-range acceleration of the force step (G m Σ r/r³ at a = 1, so the
+    physical acceleration is g/a² and the physical softening ε a) — the acceleration criterion of
+    GADGET-type codes with accuracy parameter η.  CONCEPT sorts particles into rungs by the same kind of
+    criterion on the short-range force (log lines "Determining rung population", "Rung population:",
+    TheFeedingPipeline/Datafolder4/Test_Data_concept/id0200_*/params_id0200_*.log:42,55,91-95); here
+    ALL particles take the sub-step of the highest occupied rung."""
+    if not acc2_max > 0.0:
+        return 1
+    if not math.isfinite(acc2_max):
+        raise FloatingPointError("non-finite short-range acceleration")
+    dt_allowed = math.sqrt(2.0 * eta * eps * a0 ** 3 / math.sqrt(acc2_max))
+    dlna_allowed = float(cosmo.H(a0)) * dt_allowed
+    n, span = 1, math.log(a1 / a0)
+    while n < max_sub and span / n > dlna_allowed:
+        n *= 2
+    return n
+
+
+def evolve_subcycled(stepper, cosmo: Cosmology, pos, mom, a_edges, output_at=(), on_output=None, eta=0.025,
+                     max_sub=32, stats=None):
+    """Leapfrog over `a_edges` with the long-range (mesh) force kicked once per base step and the
+    short-range (pair) force sub-cycled inside it: SURVEY §8f row 1's "rung sub-stepping" in its
+    simplest form (one rung for all particles, chosen per base step by `substep_count`).
+
+    Base step i:  mom += m g_long(x_i) ∫_{mid_{i-1}}^{mid_i} dt/a;  then n_i sub-steps over the
+    geometric subdivision of [a_i, a_{i+1}], each  mom += m g_short(x) ∫dt/a (between consecutive fine
+    midpoints);  x += mom/m ∫dt/a² (over the fine interval);  x %= L.  With n_i = 1 this is `evolve`.
+    The stepper provides accel_long(pos), accel_short(pos) (either may return None), kick(pos, mom, acc, k),
+    kick_drift(pos, mom, acc, k, d) and max_norm2(acc) -> float; `stats` (a list) receives n_i."""
+    cfg = stepper.cfg
+    if getattr(cfg, "a", 1.0) != 1.0:
+        raise ValueError("comoving time loop needs cfg.a == 1 (the a-dependence lives in the kick/drift integrals)")
+    a_edges = np.asarray(a_edges, dtype=np.float64)
+    n = a_edges.size - 1
+    mids = np.sqrt(a_edges[:-1] * a_edges[1:])
+    wanted = set(int(i) for i in output_at) | {n}
+    m = cfg.mass
+    long_mid = short_mid = float(a_edges[0])
+    for i in range(n):
+        a0, a1 = float(a_edges[i]), float(a_edges[i + 1])
+        gl = stepper.accel_long(pos)
+        if gl is not None:
+            stepper.kick(pos, mom, gl, m * cosmo.kick_factor(long_mid, float(mids[i])))
+            long_mid = float(mids[i])
+        gs = stepper.accel_short(pos)
+        if gs is None:
+            stepper.kick_drift(pos, mom, None, 0.0, cosmo.drift_factor(a0, a1) / m)
+            nsub = 1
+        else:
+            nsub = substep_count(cosmo, a0, a1, stepper.max_norm2(gs), cfg.eps, eta, max_sub)
+            fine = np.exp(np.linspace(math.log(a0), math.log(a1), nsub + 1))
+            for j in range(nsub):
+                if j > 0:
+                    gs = stepper.accel_short(pos)
+                fm = math.sqrt(fine[j] * fine[j + 1])
+                stepper.kick_drift(pos, mom, gs, m * cosmo.kick_factor(short_mid, fm),
+                                   cosmo.drift_factor(float(fine[j]), float(fine[j + 1])) / m)
+                short_mid = fm
+        if stats is not None:
+            stats.append(nsub)
+        if i + 1 in wanted:
+            p2, m2 = _clone(pos), _clone(mom)
+            gl = stepper.accel_long(p2)
+            if gl is not None:
+                stepper.kick(p2, m2, gl, m * cosmo.kick_factor(long_mid, a1))
+            gs = stepper.accel_short(p2)
+            if gs is not None:
+                stepper.kick(p2, m2, gs, m * cosmo.kick_factor(short_mid, a1))
+            if on_output is not None:
+                on_output(a1, p2, m2)
+            if i + 1 == n:
+                return p2, m2
+    return pos, mom
+
+
 class PeriodicPP:
     """Adapter for a `pp` ForceStepper inside the comoving loop: the box is periodic, so every step
     uses the nearest-image force plus the Ewald correction table (CONCEPT's periodic PP gravity)."""
@@ -86,6 +168,22 @@ class PeriodicPP:
 
     def step(self, pos, mom, dt_kick, dt_drift):
         return self.stepper.step(pos, mom, dt_kick, dt_drift, periodic_pp="ewald")
+
+    # sub-cycled loop: the whole PP force is "short range"
+    def accel_long(self, pos):
+        return None
+
+    def accel_short(self, pos):
+        return self.stepper.accel(pos, periodic_pp="ewald")
+
+    def kick(self, pos, mom, acc, k):
+        return self.stepper.kick(pos, mom, acc, k)
+
+    def kick_drift(self, pos, mom, acc, k, d):
+        return self.stepper.kick_drift(pos, mom, acc, k, d)
+
+    def max_norm2(self, acc):
+        return self.stepper.max_norm2(acc)
 
 
 def edges_through(a_begin, output_times, dlna_max=0.025):
@@ -193,7 +291,7 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
 
 
 def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_max=0.025, output_dir=None,
-             engine=None, overrides=None):
+             engine=None, overrides=None, subcycle=True, eta=0.025, max_sub=32, linear_power=None):
     """Run a CONCEPT-style `.param` file (path, text or loaded dict): ICs at a_begin, leapfrog to
     every `output_times['snapshot']` entry.  Returns [(a, pos, mom)] as host float64 arrays; with
     `output_dir` each output is also written as `snapshot_a=%.2f.hdf5` in CONCEPT's layout."""
@@ -224,7 +322,8 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
         stepper = PeriodicPP(stepper)
     lpt = int((vals.get("realization_options") or {}).get("LPT", 1))
     pos, mom = zeldovich_ics(cosmo, cfg.boxsize, n, cfg.a_begin, cfg.mass, A_s=float(prim.get("A_s", 2.1e-9)),
-                             n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt)
+                             n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt,
+                             linear_power=linear_power)
     edges, idx = edges_through(cfg.a_begin, output_times, dlna_max)
     results = []
 
@@ -236,5 +335,8 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
             snapshot.write_snapshot(os.path.join(output_dir, f"snapshot_a={a:.2f}.hdf5"), hp, hm, boxsize=cfg.boxsize,
                                     a=a, mass=cfg.mass, H0=cfg.H0, Omega_b=cfg.Omega_b, Omega_cdm=cfg.Omega_cdm)
 
-    evolve(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit)
+    if subcycle and cfg.method in ("p3m", "pp"):
+        evolve_subcycled(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit, eta=eta, max_sub=max_sub)
+    else:
+        evolve(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit)
     return results

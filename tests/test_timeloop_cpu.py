@@ -195,3 +195,94 @@ def test_loop_argument_errors():
                         on_output=lambda s, p, m: seen.append(s))
     b = timeloop.evolve(OracleStepper(cfg), c, pos, mom, edges)
     assert len(seen) == 3 and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+class SplitOracleStepper(OracleStepper):
+    """numpy stand-in with ForceStepper's split interface (in-place updates like the device tensors)."""
+
+    def accel_long(self, pos):
+        c = self.cfg
+        if c.method == "pp":
+            return None
+        return oforce.pm_accel(pos, c.boxsize, c.gridsize, G=c.G, mass=c.mass, r_s=c.r_s, deconv_order=c.deconv_order,
+                               interlace=bool(c.interlace[0]), interlace_down=bool(c.interlace[1]))
+
+    def accel_short(self, pos):
+        c = self.cfg
+        if c.method == "pm":
+            return None
+        if c.method == "pp":
+            return oforce.pp_accel(pos, c.boxsize, c.G, c.mass, c.eps, True)
+        return oforce.p3m_short_accel(pos, c.boxsize, c.r_s, c.r_cut, c.G, c.mass, c.eps)
+
+    def kick(self, pos, mom, acc, k):
+        mom += acc * k
+
+    def kick_drift(self, pos, mom, acc, k, d):
+        if acc is not None:
+            mom += acc * k
+        pos += mom * d
+        pos %= self.cfg.boxsize
+
+    def max_norm2(self, acc):
+        return float((acc * acc).sum(1).max())
+
+
+def test_substep_count_criterion():
+    """n = smallest power of two with Δt_base/n <= sqrt(2 η ε a³ / |g|max): closed-form cases."""
+    c = Cosmology()
+    a0, a1, eps, eta = 0.5, 0.5 * math.exp(0.025), 0.2, 0.025
+    dt_base = 0.025 / float(c.H(a0))
+    g1 = 2 * eta * eps * a0 ** 3 / dt_base ** 2            # acceleration that allows exactly the base step
+    assert timeloop.substep_count(c, a0, a1, 0.0, eps) == 1
+    assert timeloop.substep_count(c, a0, a1, (0.99 * g1) ** 2, eps, eta) == 1
+    assert timeloop.substep_count(c, a0, a1, (1.01 * g1) ** 2, eps, eta) == 2
+    assert timeloop.substep_count(c, a0, a1, (15.0 * g1) ** 2, eps, eta) == 4       # sqrt(15) < 4
+    assert timeloop.substep_count(c, a0, a1, (17.0 * g1) ** 2, eps, eta) == 8
+    assert timeloop.substep_count(c, a0, a1, (1e9 * g1) ** 2, eps, eta, max_sub=16) == 16
+    import pytest
+    with pytest.raises(FloatingPointError):
+        timeloop.substep_count(c, a0, a1, float("inf"), eps)
+
+
+def _clustered_set(n, L, seed):
+    rs = np.random.RandomState(seed)
+    centres = rs.random_sample((6, 3)) * L
+    pos = centres[rs.randint(0, 6, n)] + rs.normal(scale=0.05 * L, size=(n, 3))
+    return pos % L
+
+
+def test_subcycled_loop_equals_plain_loop_without_substeps_and_converges_with_them():
+    """(1) max_sub = 1 reproduces `evolve` exactly for P3M (same kicks, same drifts); a PM run never
+    sub-cycles.  (2) On a clustered set the sub-cycled loop is closer to a much finer uniform run than the
+    plain loop with the same base steps (reference: 64x finer uniform steps), and it takes more than one sub-step where the short-range
+    acceleration demands it."""
+    c = Cosmology()
+    L, n, N = 60.0, 216, 8
+    rho_m = 3 * c.H0 ** 2 / (8 * math.pi * G_NEWTON) * c.Omega_m
+    mass = rho_m * L ** 3 / n * 3.0                       # overdense: short dynamical times
+    pos = _clustered_set(n, L, 2)
+    mom = np.zeros_like(pos)
+    for method in ("p3m", "pm"):
+        cfg = ForceConfig(method=method, npart=n, boxsize=L, gridsize=N, interlace=(True, True), deconvolve=(True, True),
+                          G=G_NEWTON, mass=mass, softening_frac=0.05)
+        edges = scale_factor_edges(0.5, 0.6, 0.03)
+        p0, m0 = timeloop.evolve(OracleStepper(cfg), c, pos.copy(), mom.copy(), edges)
+        stats = []
+        p1, m1 = timeloop.evolve_subcycled(SplitOracleStepper(cfg), c, pos.copy(), mom.copy(), edges, max_sub=1,
+                                           stats=stats)
+        assert stats == [1] * (len(edges) - 1)
+        assert np.abs((p1 - p0 + L / 2) % L - L / 2).max() < 1e-9 * L and np.abs(m1 - m0).max() < 1e-9 * np.abs(m0).max()
+    cfg = ForceConfig(method="p3m", npart=n, boxsize=L, gridsize=N, interlace=(True, True), deconvolve=(True, True),
+                      G=G_NEWTON, mass=mass, softening_frac=0.05)
+    edges = scale_factor_edges(0.5, 0.6, 0.03)
+    fine = scale_factor_edges(0.5, 0.6, 0.03 / 64)
+    pf, mf = timeloop.evolve(OracleStepper(cfg), c, pos.copy(), mom.copy(), fine)
+    p0, m0 = timeloop.evolve(OracleStepper(cfg), c, pos.copy(), mom.copy(), edges)
+    stats = []
+    ps, ms = timeloop.evolve_subcycled(SplitOracleStepper(cfg), c, pos.copy(), mom.copy(), edges, eta=0.025, max_sub=32,
+                                       stats=stats)
+    assert max(stats) > 1 and all(s & (s - 1) == 0 for s in stats)
+    err_plain = np.abs(m0 - mf).max()
+    err_sub = np.abs(ms - mf).max()
+    assert err_sub < 0.5 * err_plain, (err_sub, err_plain, stats)

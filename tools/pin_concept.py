@@ -87,7 +87,7 @@ def force_cfg(method, n, L, cosmo, mesh=None):
 
 
 # ------------------------------------------------------------------------------------ back ends
-def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
+def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.25, est_interlace=True, sub=None):
     """ICs, leapfrog and estimator on the device (the product path)."""
     import torch
     from nbody_b200 import api, force as F
@@ -95,7 +95,7 @@ def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
     eng = default_engine()
     c1, c2 = api._draws(n, None, None, seed)
     pos, mom = timeloop.zeldovich_ics(cosmo, L, n, cfg.a_begin, cfg.mass, c1=c1, c2=c2, engine=eng, lpt=lpt,
-                                      linear_power=lin)
+                                      linear_power=lin, lattice_offset=offset)
     noise2 = np.abs(api.createR(n, c1=c1, c2=c2, guard=True)) ** 2
     stepper = F.ForceStepper(cfg, eng)
     if cfg.method == "pp":
@@ -105,15 +105,20 @@ def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
 
     def emit(a, p, m):
         g = (cosmo.growth(a) / cosmo.growth(1.0)) ** 2
-        ps = PS.concept_powerspec(p, L, n, linear=lambda k: g * lin(k), noise_abs2=noise2,
+        ps = PS.concept_powerspec(p, L, n, linear=lambda k: g * lin(k), noise_abs2=noise2, interlace=est_interlace,
                                   tophat=8.0 / cosmo.h, a=a, t=cosmo.cosmic_time(a), engine=eng)
         out[round(a, 6)] = (ps, float(torch.sqrt((m ** 2).mean()).item()))
 
-    timeloop.evolve(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit)
-    return out, len(edges) - 1
+    stats = []
+    if sub and cfg.method != "pm":
+        timeloop.evolve_subcycled(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit, eta=sub[0],
+                                  max_sub=sub[1], stats=stats)
+    else:
+        timeloop.evolve(stepper, cosmo, pos, mom, edges, output_at=idx, on_output=emit)
+    return out, (len(edges) - 1, int(sum(stats)) if stats else len(edges) - 1)
 
 
-def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
+def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.25, est_interlace=True, sub=None):
     """Same run with the float64 oracle: numpy ICs, C/numpy force loop, numpy estimator."""
     from oracle import concept_ps, cpu_step, restate
     if lpt != 1:
@@ -126,16 +131,42 @@ def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
     _, psi = restate.grf_delta_psi(pk, R, L, n)
     psi = np.stack([p.ravel() for p in psi], axis=1)
     d_rel = cosmo.growth(cfg.a_begin) / cosmo.growth(1.0)
-    q = restate.lattice(L, n) + 0.25 * L / n
+    q = restate.lattice(L, n) + offset * L / n
     pos = (q + d_rel * psi) % L
     mom = cfg.mass * cfg.a_begin ** 2 * float(cosmo.H(cfg.a_begin)) * cosmo.growth_rate(cfg.a_begin) * d_rel * psi
 
+    from oracle import cport, force as oforce
+
     class Stepper:
+        """numpy stand-in with ForceStepper's interface (in-place updates like the device tensors)."""
+
         def __init__(self):
             self.cfg = cfg
 
         def step(self, p, m, dk, dd):
             return cpu_step.step(cfg, p, m, dk, dd)
+
+        def accel_long(self, p):
+            return None if cfg.method == "pp" else cpu_step.pm_accel(cfg, p)
+
+        def accel_short(self, p):
+            if cfg.method == "pm":
+                return None
+            if cfg.method == "pp":
+                return oforce.pp_accel_ewald(p, L, cfg.G, cfg.mass, cfg.eps)
+            return cport.p3m_short_accel(p, L, cfg.r_s, cfg.r_cut, cfg.G, cfg.mass, cfg.eps)
+
+        def kick(self, p, m, acc, k):
+            m += acc * k
+
+        def kick_drift(self, p, m, acc, k, d):
+            if acc is not None:
+                m += acc * k
+            p += m * d
+            p %= L
+
+        def max_norm2(self, acc):
+            return float((acc * acc).sum(1).max())
 
     geom = PS.bin_geometry(n)
     ranges = [(int(f), int(l)) for f, l in zip(geom.first_k2, list(geom.first_k2[1:] - 1) + [geom.k2_end - 1])]
@@ -144,7 +175,7 @@ def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
 
     def emit(a, p, m):
         g = (cosmo.growth(a) / cosmo.growth(1.0)) ** 2
-        modes, P = concept_ps.powerspec(p, L, n, ranges)
+        modes, P = concept_ps.powerspec(p, L, n, ranges, interlace=est_interlace)
         ratio = concept_ps.noise_ratio(R, L, n, ranges, lin)
         linc, _ = PS.linear_column(geom, L, lambda k: g * lin(k))
         ps = PS.PowerSpec(2 * math.pi / L * geom.k_grid, modes, P, corrected=P * ratio, linear=linc, gridsize=n,
@@ -152,8 +183,13 @@ def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt):
         ps.sigma = tuple(PS.sigma_tophat(ps.k, c, ps.tophat) for c in ps.columns())
         out[round(a, 6)] = (ps, float(np.sqrt((m ** 2).mean())))
 
-    timeloop.evolve(Stepper(), cosmo, pos, mom, edges, output_at=idx, on_output=emit)
-    return out, len(edges) - 1
+    stats = []
+    if sub and cfg.method != "pm":
+        timeloop.evolve_subcycled(Stepper(), cosmo, pos, mom, edges, output_at=idx, on_output=emit, eta=sub[0],
+                                  max_sub=sub[1], stats=stats)
+    else:
+        timeloop.evolve(Stepper(), cosmo, pos, mom, edges, output_at=idx, on_output=emit)
+    return out, (len(edges) - 1, int(sum(stats)) if stats else len(edges) - 1)
 
 
 # ------------------------------------------------------------------------------------ driver
@@ -167,11 +203,16 @@ def main(argv=None):
     ap.add_argument("--dlna", type=float, default=0.025)
     ap.add_argument("--lpt", type=int, default=1)
     ap.add_argument("--softening", type=float, default=None, help="Plummer ε in units of L/cbrt(N)")
+    ap.add_argument("--eta", type=float, default=0.025, help="accuracy parameter of the sub-step criterion")
+    ap.add_argument("--max-sub", type=int, default=32, help="largest number of short-range sub-steps per base step; 1: off")
+    ap.add_argument("--lattice-offset", type=float, default=0.25, help="IC lattice offset in particle spacings")
+    ap.add_argument("--estimator-interlace", type=int, default=1, help="0: estimator without interlacing")
     ap.add_argument("--out", default=None)
     a = ap.parse_args(argv)
     cosmo = Cosmology()
     run = run_gpu if a.backend == "gpu" else run_cpu
-    report = {"backend": a.backend, "n": a.n, "dlna_max": a.dlna, "seeds": a.seeds, "lpt": a.lpt, "runs": {}}
+    report = {"backend": a.backend, "n": a.n, "dlna_max": a.dlna, "seeds": a.seeds, "lpt": a.lpt,
+              "lattice_offset": a.lattice_offset, "eta": a.eta, "max_sub": a.max_sub, "estimator_interlace": bool(a.estimator_interlace), "runs": {}}
     spectra = {}
     for meth in a.methods.split(","):
         if meth == "snapvspk":
@@ -186,7 +227,8 @@ def main(argv=None):
         acc = {round(o, 6): [] for o in outs}
         t0 = time.time()
         for s in range(a.seeds):
-            res, nsteps = run(cfg, cosmo, a.n, L, lin, a.seed0 + s, outs, a.dlna, a.lpt)
+            res, (nsteps, nshort) = run(cfg, cosmo, a.n, L, lin, a.seed0 + s, outs, a.dlna, a.lpt, a.lattice_offset,
+                                        bool(a.estimator_interlace), (a.eta, a.max_sub) if a.max_sub > 1 else None)
             for k, v in res.items():
                 acc[k].append(v)
         wall = time.time() - t0
@@ -196,7 +238,8 @@ def main(argv=None):
             Pc = np.array([g[0].corrected for g in got])
             sig = np.array([g[0].sigma for g in got])
             rec = {
-                "method": method, "boxsize": L, "a": o, "steps": nsteps, "wall_s": round(wall, 2),
+                "method": method, "boxsize": L, "a": o, "steps": nsteps, "short_range_evaluations": nshort,
+                "wall_s": round(wall, 2),
                 "modes_exact": bool(np.array_equal(got[0][0].modes, ref.modes)),
                 "k_8_significant_figures": bool(all("%.7e" % x == "%.7e" % y for x, y in zip(got[0][0].k, ref.k))),
                 "linear_column_max_rel": float(np.abs(got[0][0].linear / ref.linear - 1).max()),
@@ -211,7 +254,7 @@ def main(argv=None):
             report["runs"][tag] = rec
             spectra[tag] = Pc.mean(0)
             r = np.array(rec["P_corrected_over_ref_corrected"])
-            print(f"{tag}: steps {nsteps}, {wall:.1f} s, modes exact {rec['modes_exact']}, k exact "
+            print(f"{tag}: steps {nsteps} ({nshort} short-range), {wall:.1f} s, modes exact {rec['modes_exact']}, k exact "
                   f"{rec['k_8_significant_figures']}, sigma8 {sig.mean(0)[0]:.4f} (ref {ref.sigma[0]:.3f}), "
                   f"corrected P / ref: {np.array2string(r, precision=3)}", flush=True)
     if "P3M_a=1.00" in spectra and "PM_a=1.00" in spectra:
