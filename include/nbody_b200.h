@@ -250,6 +250,8 @@ int nb_pp_accel_ewald(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void
  *   u = r/(2 r_s), t = 2u²/u_max² - 1, Q given by ncoef = 11 monomial coefficients (host).
  * i_limit > 0: particles with perm >= i_limit are sources only (halo copies of another slab's
  * particles in a multi-GPU run; their acc rows are not touched); 0 = every particle.
+ * Only the acc rows of i-particles that live in [cell_lo, cell_hi) are written (accumulate = 0) or added
+ * to (accumulate = 1): with a partial or empty cell range the caller zeroes the other rows itself.
  * sorted_xyzw.w must be the uniform mass nb_cell_sort writes. */
 int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
                  void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream);

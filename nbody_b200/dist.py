@@ -268,7 +268,7 @@ class SlabMesh:
                       for _ in range(2 if (nb_fwd > 1 or nc_inv > 1) else 1)]
         self.xbuf = self.xbufs[0]
         self.rhok = torch.empty((nb_fwd, N, lay.nyl, lay.nzh), dtype=torch.complex64, device=dev)
-        self.n_outside = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.n_outside = torch.zeros(max(nb_fwd, 1), dtype=torch.int64, device=dev)   # per deposit pass
         if nc_inv:
             self.g = torch.empty((nc_inv, N, lay.nyl, lay.nzh), dtype=torch.complex64, device=dev)
             self.force = torch.empty((nc_inv, npl, N, N), dtype=torch.float32, device=dev)
@@ -279,11 +279,21 @@ class SlabMesh:
         lay, eng = self.lay, self.eng
         for b in range(nb):
             eng.cic_deposit_slab(pos, self.cell, self.N, lay.x0, lay.nxl, lay.n_ghost, self.rho[b],
-                                 shift=0.5 * self.cell * b, n_outside=self.n_outside)
+                                 shift=0.5 * self.cell * b, n_outside=self.n_outside[b:b + 1])
         tx = self.rho[:nb, lay.nxl:].contiguous()
         self.comm.shift(tx, self.ghost_rx[:nb], +1)
         for b in range(nb):
             eng.grid_add(self.rho[b, :lay.n_ghost], self.ghost_rx[b])
+
+    def check_outside(self):
+        """Raise if the last deposit was handed particles outside this rank's x-slab: the slab kernels
+        give them zero mass and zero mesh force, so a wrong sharding would otherwise go unnoticed
+        (one host sync; the step folds the same counter into migrate()'s existing sync)."""
+        n = int(self.n_outside.sum().item())
+        if n:
+            from ._lib import NbodyError
+            raise NbodyError(f"{n} particle(s) of rank {self.comm.rank} lie outside its x-slab "
+                             "(shard with dist.shard_particles / keep the set returned by step())")
 
     # real x-slab b -> y-slab spectrum rhok[b]  ([N][nyl][nzh])
     def forward(self, b: int):
@@ -485,9 +495,15 @@ class DistForceStepper:
             return pos, mom
         n = pos.shape[0]
         owner, counts = self.eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world)
-        moved = (n - counts[self.rank]).reshape(1).clone()
+        # leavers of this step and the particles the deposit found outside the slab (wrong sharding on entry)
+        moved = torch.stack([n - counts[self.rank], self.mesh.n_outside.sum()])
         self.comm.all_reduce(moved, "max")
-        if int(moved.item()) == 0:                                  # host sync, once per step
+        n_moved, n_out_slab = (int(v) for v in moved.tolist())      # host sync, once per step
+        if n_out_slab:
+            from ._lib import NbodyError
+            raise NbodyError(f"{n_out_slab} particle(s) were outside their rank's x-slab at the deposit of this step "
+                             "(shard with dist.shard_particles / keep the set returned by step())")
+        if n_moved == 0:
             return pos, mom
         out_idx = (owner != self.rank).nonzero().squeeze(1)        # ascending
         dest = owner[out_idx]
@@ -530,6 +546,8 @@ class DistForceStepper:
         if self.world > 1 and c.method == "p3m":
             pos, _ = self._own(pos)
         self.pm_mesh(pos)
+        if self.world > 1:
+            self.mesh.check_outside()
         self._gather(pos, None, acc, 0.0, 0.0)
         if c.method == "p3m":
             self.short_range(pos, acc, accumulate=True)
@@ -577,10 +595,12 @@ class DistPowerSpectrum:
         self.counts = torch.zeros(n_edges - 1, dtype=torch.int64, device=engine.device)
         self.sums = torch.zeros(n_edges - 1, dtype=torch.float64, device=engine.device)
 
-    def __call__(self, pos, n_total: int, mark=None):
+    def __call__(self, pos, n_total: int, mark=None, check=True):
         mark = mark or (lambda name, fn: fn())
         m, N, L = self.mesh, self.N, self.L
         mark("deposit + ghost add", lambda: m.deposit(pos, 1))
+        if check and self.comm.world > 1:
+            m.check_outside()
         own = m.rho[0, :m.lay.nxl]
         mark("overdensity", lambda: self.eng.grid_affine(own, a=(L / N) ** 3, b=n_total / L ** 3, c=1.0))
         mark("slab fft + all-to-all", lambda: m.forward(0))

@@ -252,15 +252,16 @@ def second_order_displacement(delta, L):
 
 
 def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649, seed=None, c1=None, c2=None,
-                  engine=None, lattice_offset=0.25, lpt=1, linear_power=None):
+                  engine=None, lattice_offset=0.5, lpt=1, linear_power=None):
     """1LPT initial conditions on the device: (pos, mom) float64 (n³,3) tensors at a_begin.
     ψ(a=1) comes from nb_grf_synthesize on the particle lattice (grid nodes = lattice sites, no
     gather needed); x = q + D₊ψ (wrapped), mom = m a² H f D₊ ψ with D₊ normalised to 1 at a = 1.
-    `lattice_offset` (in particle spacings) moves the whole lattice off the mesh nodes: with
-    mesh = cbrt(N) a particle ON a node sits at the kink of the CIC weight and the mesh force
-    responds to a small displacement like |dx|, which shows up as 1-3 % errors in the growth of the
-    lowest modes; a quarter spacing is smooth for both the plain and the interlaced (half-cell
-    shifted) grid.  0 gives the reference's `particle_assigment` lattice (Power_compare.py:340-345).
+    `lattice_offset` (in particle spacings) places the lattice relative to the mesh nodes.  The default
+    0.5 (particles at the cell centres of a cbrt(N) mesh) is what the reference's CONCEPT runs are matched
+    by: with it the 64³ runs reproduce the reference's `powerspec_a=*` files to ±2.3 % per bin at a = 0.17
+    and ±4-6 % at a = 1 up to the Nyquist frequency, while 0.25 loses 30-55 % of the power near Nyquist
+    and 0 (particles ON the nodes, the kink of the CIC weight; the reference's `particle_assigment`
+    lattice, Power_compare.py:340-345) gains 20-35 % there (tools/pin_concept.py).
     `lpt=2` adds the second-order term D₂ψ⁽²⁾ (`realization_options['LPT']`, Giant.param:70-72; the
     reference compares both orders in 1LPTvs2LPT/1vs2tlptplotter.py)."""
     import torch

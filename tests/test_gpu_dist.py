@@ -147,3 +147,30 @@ def test_deposit_slab_reports_foreign_particles():
     nout = torch.zeros(1, dtype=torch.int64, device=eng.device)
     eng.cic_deposit_slab(pos, L / N, N, 0, 4, 2, grid, n_outside=nout)
     assert int(nout.item()) == 1 and abs(float(grid.sum().item()) - 1.0) < 1e-6
+
+
+def test_wrongly_sharded_particles_are_reported():
+    """A particle handed to the wrong rank gets zero mass and zero mesh force from the slab kernels; both
+    accel() and step() must raise instead of returning wrong physics."""
+    from nbody_b200._lib import NbodyError
+    L, n, N, world = 1000.0, 16, 32, 2
+    pos = zeldovich_particles(n, L, seed=11)
+    cfg = cfg_for("pm", n, N, L, interlace=(True, True), deconvolve=(True, True), G=1.0, mass=2.0)
+    own = owner_np(pos, L, N, world)
+    bad = int(np.nonzero(own == 1)[0][0])                # give one of rank 1's particles to rank 0 as well
+
+    def fn(st, p, i):
+        if st.rank == 0:
+            p = torch.cat([p, st.eng.to_device(pos[bad:bad + 1])])
+        out = []
+        for call in (lambda: st.accel(p), lambda: st.step(p.clone(), torch.zeros_like(p), 1e-3, 1e-3)):
+            try:
+                call()
+                out.append("ok")
+            except NbodyError:
+                out.append("raised")
+        return out
+
+    res, _ = run_ranks(world, cfg, pos, fn)
+    assert res[0][0] == "raised"                          # accel(): the rank that holds the stray particle
+    assert res[0][1] == "raised" and res[1][1] == "raised"   # step(): the count is all-reduced in migrate()

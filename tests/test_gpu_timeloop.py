@@ -37,7 +37,7 @@ def test_zeldovich_ics_match_the_numpy_restatement():
     assert np.abs(mom.cpu().numpy() - mom_ref).max() <= 1e-10 * np.abs(mom_ref).max()
     # the reference's own lattice (no offset) is available too
     pos0, _ = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lattice_offset=0.0)
-    assert _pdiff(pos0.cpu().numpy(), (pos_ref - 0.25 * L / n) % L, L) <= 1e-10 * L
+    assert _pdiff(pos0.cpu().numpy(), (pos_ref - 0.5 * L / n) % L, L) <= 1e-10 * L
 
 
 def test_second_order_ics_match_the_numpy_restatement():

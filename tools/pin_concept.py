@@ -87,7 +87,7 @@ def force_cfg(method, n, L, cosmo, mesh=None):
 
 
 # ------------------------------------------------------------------------------------ back ends
-def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.25, est_interlace=True, sub=None):
+def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_interlace=True, sub=None):
     """ICs, leapfrog and estimator on the device (the product path)."""
     import torch
     from nbody_b200 import api, force as F
@@ -118,7 +118,7 @@ def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.25, est_int
     return out, (len(edges) - 1, int(sum(stats)) if stats else len(edges) - 1)
 
 
-def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.25, est_interlace=True, sub=None):
+def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_interlace=True, sub=None):
     """Same run with the float64 oracle: numpy ICs, C/numpy force loop, numpy estimator."""
     from oracle import concept_ps, cpu_step, restate
     if lpt != 1:
@@ -205,7 +205,7 @@ def main(argv=None):
     ap.add_argument("--softening", type=float, default=None, help="Plummer ε in units of L/cbrt(N)")
     ap.add_argument("--eta", type=float, default=0.025, help="accuracy parameter of the sub-step criterion")
     ap.add_argument("--max-sub", type=int, default=32, help="largest number of short-range sub-steps per base step; 1: off")
-    ap.add_argument("--lattice-offset", type=float, default=0.25, help="IC lattice offset in particle spacings")
+    ap.add_argument("--lattice-offset", type=float, default=0.5, help="IC lattice offset in particle spacings")
     ap.add_argument("--estimator-interlace", type=int, default=1, help="0: estimator without interlacing")
     ap.add_argument("--out", default=None)
     a = ap.parse_args(argv)
