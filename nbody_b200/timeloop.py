@@ -252,16 +252,19 @@ def second_order_displacement(delta, L):
 
 
 def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649, seed=None, c1=None, c2=None,
-                  engine=None, lattice_offset=0.5, lpt=1, linear_power=None):
+                  engine=None, lattice_offset=0.0, lpt=1, linear_power=None):
     """1LPT initial conditions on the device: (pos, mom) float64 (n³,3) tensors at a_begin.
     ψ(a=1) comes from nb_grf_synthesize on the particle lattice (grid nodes = lattice sites, no
     gather needed); x = q + D₊ψ (wrapped), mom = m a² H f D₊ ψ with D₊ normalised to 1 at a = 1.
-    `lattice_offset` (in particle spacings) places the lattice relative to the mesh nodes.  The default
-    0.5 (particles at the cell centres of a cbrt(N) mesh) is what the reference's CONCEPT runs are matched
-    by: with it the 64³ runs reproduce the reference's `powerspec_a=*` files to ±2.3 % per bin at a = 0.17
-    and ±4-6 % at a = 1 up to the Nyquist frequency, while 0.25 loses 30-55 % of the power near Nyquist
-    and 0 (particles ON the nodes, the kink of the CIC weight; the reference's `particle_assigment`
-    lattice, Power_compare.py:340-345) gains 20-35 % there (tools/pin_concept.py).
+    `lattice_offset` (in particle spacings) places the lattice relative to the mesh nodes.  The default 0
+    puts the particles ON the nodes of a cbrt(N) mesh: the reference's own lattice (`particle_assigment`,
+    Power_compare.py:340-345) and the placement of its CONCEPT runs (the mean of exp(2πi x/h) over the
+    particles of the shipped a = 1 snapshots has phase 0.000 for the vertex-centred Giant.param runs and
+    ≈ 0.5 for the cell-centred NN.param runs: on the value points of the grid in both).  With the
+    interlaced mesh pair 0 and 0.5 are equivalent; they reproduce the reference's `powerspec_a=*` files
+    to ±2.3 % per bin at a = 0.17 and ±4-6 % at a = 1 up to the Nyquist frequency.  A quarter spacing
+    (smooth CIC response on both meshes, 1-3 % more growth of the lowest modes) loses 30-55 % of the
+    reference's power near the Nyquist frequency (tools/pin_concept.py).
     `lpt=2` adds the second-order term D₂ψ⁽²⁾ (`realization_options['LPT']`, Giant.param:70-72; the
     reference compares both orders in 1LPTvs2LPT/1vs2tlptplotter.py)."""
     import torch
@@ -292,7 +295,7 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
 
 
 def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_max=0.025, output_dir=None,
-             engine=None, overrides=None, subcycle=True, eta=0.025, max_sub=32, linear_power=None):
+             engine=None, overrides=None, subcycle=True, eta=0.025, max_sub=32, linear_power=None, lattice_offset=0.0):
     """Run a CONCEPT-style `.param` file (path, text or loaded dict): ICs at a_begin, leapfrog to
     every `output_times['snapshot']` entry.  Returns [(a, pos, mom)] as host float64 arrays; with
     `output_dir` each output is also written as `snapshot_a=%.2f.hdf5` in CONCEPT's layout."""
@@ -324,7 +327,7 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
     lpt = int((vals.get("realization_options") or {}).get("LPT", 1))
     pos, mom = zeldovich_ics(cosmo, cfg.boxsize, n, cfg.a_begin, cfg.mass, A_s=float(prim.get("A_s", 2.1e-9)),
                              n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt,
-                             linear_power=linear_power)
+                             linear_power=linear_power, lattice_offset=lattice_offset)
     edges, idx = edges_through(cfg.a_begin, output_times, dlna_max)
     results = []
 

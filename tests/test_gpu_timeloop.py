@@ -35,9 +35,9 @@ def test_zeldovich_ics_match_the_numpy_restatement():
     pos, mom = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2)
     assert _pdiff(pos.cpu().numpy(), pos_ref, L) <= 1e-10 * L
     assert np.abs(mom.cpu().numpy() - mom_ref).max() <= 1e-10 * np.abs(mom_ref).max()
-    # the reference's own lattice (no offset) is available too
-    pos0, _ = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lattice_offset=0.0)
-    assert _pdiff(pos0.cpu().numpy(), (pos_ref - 0.5 * L / n) % L, L) <= 1e-10 * L
+    # the default is the reference's own lattice (no offset); any other placement is a shift of it
+    pos0, _ = timeloop.zeldovich_ics(c, L, n, a0, cfg.mass, c1=c1, c2=c2, lattice_offset=0.25)
+    assert _pdiff(pos0.cpu().numpy(), (pos_ref + 0.25 * L / n) % L, L) <= 1e-10 * L
 
 
 def test_second_order_ics_match_the_numpy_restatement():
@@ -137,7 +137,13 @@ def test_param_driven_run_grows_linearly_at_low_k_and_writes_snapshots(tmp_path)
     growth = (c.growth(1.0) / c.growth(0.5)) ** 2
     ratio = p_one[low] / p_half[low]
     print("P(a=1)/P(a=0.5) over linear growth:", np.round(ratio / growth, 3))
-    assert np.abs(np.median(ratio) / growth - 1) < 0.05 and np.abs(ratio / growth - 1).max() < 0.20
+    # particles start ON the mesh nodes (CONCEPT's placement, the one the reference's powerspec files are
+    # matched by): the lowest modes then grow 2-4 % less than linear theory in amplitude (median 0.94 in power,
+    # measured); the quarter-cell placement is within 5 % but does not reproduce the reference's runs
+    assert np.abs(np.median(ratio) / growth - 1) < 0.09 and np.abs(ratio / growth - 1).max() < 0.20
+    res_q = timeloop.simulate(PARAM, seed=3, dlna_max=0.025, lattice_offset=0.25)
+    pq = [api.power_spectrum_from_positions(pos, L, n, deconvolve=True)[1] for _a, pos, _m in res_q]
+    assert np.abs(np.median(pq[1][low] / pq[0][low]) / growth - 1) < 0.05
     # against the linear spectrum itself: band-averaged over the low bins (few modes per bin)
     lin = c.linear_power(k[low])
     assert abs(np.mean(p_one[low] / lin) - 1) < 0.35

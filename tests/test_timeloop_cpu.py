@@ -24,7 +24,7 @@ class OracleStepper:
                                  dt_kick=dt_kick, dt_drift=dt_drift)
 
 
-def numpy_zeldovich(cosmo, L, n, a_begin, mass, seed, A_s=2.1e-9, n_s=0.9649, lattice_offset=0.5):
+def numpy_zeldovich(cosmo, L, n, a_begin, mass, seed, A_s=2.1e-9, n_s=0.9649, lattice_offset=0.0):
     """Numpy restatement of timeloop.zeldovich_ics (same draws, same conventions)."""
     pk = timeloop.linear_pk_grid(cosmo, L, n, A_s, n_s)
     rs = np.random.RandomState(seed)
@@ -96,9 +96,9 @@ def test_leapfrog_reproduces_linear_growth_with_the_oracle_force():
                       deconvolve=(True, True), G=G_NEWTON, mass=mass)
     a0, a1 = 0.02, 0.2
     # A_s 100x below Giant.param's keeps second-order mode coupling out of the comparison
-    # quarter-cell offset: the cleanest linear response (see the docstring); at the product's default of half a
-    # cell (particles on the nodes of the interlaced mesh, CONCEPT's placement by the full-run pin) the same
-    # low modes are 2.8 % off at this tiny amplitude
+    # quarter-cell offset: the cleanest linear response (see the docstring); at the product's default (particles
+    # ON the mesh nodes, CONCEPT's placement by the full-run pin) the same low modes are 2.8 % off at this
+    # tiny amplitude
     pos, mom, psi, q, _ = numpy_zeldovich(c, L, n, a0, mass, seed=5, A_s=2.1e-11, lattice_offset=0.25)
     outs = []
     p1, m1 = timeloop.evolve(OracleStepper(cfg), c, pos, mom, scale_factor_edges(a0, a1, 0.05),

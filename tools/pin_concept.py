@@ -55,8 +55,8 @@ RUNS = {
 class TabulatedLinear:
     """Linear P(k, a=1) whose mode-averaged bin means equal the `P_linear` column of a reference file:
     the closed-form spectrum of cosmo.py (Eisenstein-Hu with baryons, standing in for CLASS) times a
-    correction interpolated linearly in ln k through the 16 bins, constant outside them.  Two
-    fixed-point passes make the binned mean match the column to < 1e-4."""
+    correction interpolated linearly in ln k through the 16 bins, constant outside them.  Fixed-point
+    passes make the binned mean match the column to < 1e-6."""
 
     def __init__(self, cosmo, ref: PS.PowerSpec, boxsize, a_file=1.0, A_s=2.105e-9, n_s=0.9649):
         self.cosmo, self.A_s, self.n_s = cosmo, A_s, n_s
@@ -64,7 +64,7 @@ class TabulatedLinear:
         self.corr = np.ones(ref.k.size)
         geom = PS.bin_geometry(ref.gridsize or 64)
         target = ref.linear / (cosmo.growth(a_file) / cosmo.growth(1.0)) ** 2
-        for _ in range(4):
+        for _ in range(24):
             have, _p = PS.linear_column(geom, boxsize, self)
             self.corr *= target / have
         self.residual = float(np.abs(PS.linear_column(geom, boxsize, self)[0] / target - 1).max())
@@ -87,7 +87,7 @@ def force_cfg(method, n, L, cosmo, mesh=None):
 
 
 # ------------------------------------------------------------------------------------ back ends
-def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_interlace=True, sub=None):
+def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.0, est_interlace=True, sub=None):
     """ICs, leapfrog and estimator on the device (the product path)."""
     import torch
     from nbody_b200 import api, force as F
@@ -118,7 +118,7 @@ def run_gpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_inte
     return out, (len(edges) - 1, int(sum(stats)) if stats else len(edges) - 1)
 
 
-def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_interlace=True, sub=None):
+def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.0, est_interlace=True, sub=None):
     """Same run with the float64 oracle: numpy ICs, C/numpy force loop, numpy estimator."""
     from oracle import concept_ps, cpu_step, restate
     if lpt != 1:
@@ -192,6 +192,50 @@ def run_cpu(cfg, cosmo, n, L, lin, seed, a_outs, dlna, lpt, offset=0.5, est_inte
     return out, (len(edges) - 1, int(sum(stats)) if stats else len(edges) - 1)
 
 
+def giant32(a, cosmo, run):
+    """The reference's two 32³, L = 1000 Mpc, a = 1 snapshots (Different_Sizes/newrun2/3giant32{pm,p3m},
+    Giant.param with _size = 32: A_s = 2.1e-9) hold positions AND momenta: compare the rms momentum of our
+    runs of the same set-up (mean over seeds) and, for P³M, the estimator's P(k) of the reference's
+    particle positions with that of ours (32³: 10 bins, cosmic variance of single realisations on both sides)."""
+    d = np.load(os.path.join(ROOT, "tests", "golden", "snap_giant32_mom.npz"))
+    n, L = 32, 1000.0
+    ref100 = PS.read_powerspec(os.path.join(GOLD, "SnapVsPK_a=1.00.txt"))
+    lin0 = TabulatedLinear(cosmo, ref100, L, a_file=1.0)                 # CLASS shape of the L = 1000 file ...
+    lin = lambda k: lin0(k) * (2.1e-9 / 2.105e-9)                        # noqa: E731  ... at Giant.param's A_s
+    out = {}
+    for method in ("pm", "p3m"):
+        cfg = force_cfg(method, n, L, cosmo)
+        if a.deconv_order is not None:
+            cfg.deconvolve = (a.deconv_order >= 1, a.deconv_order >= 2)
+        rms, P = [], []
+        for s in range(a.seeds):
+            res, _ = run(cfg, cosmo, n, L, lin, a.seed0 + s, [1.0], a.dlna, a.lpt, a.lattice_offset,
+                         bool(a.estimator_interlace), (a.eta, a.max_sub) if a.max_sub > 1 else None)
+            ps, r = res[1.0]
+            rms.append(r)
+            P.append(ps.power)
+        ref_rms = float(np.sqrt((d[f"mom_{method}"] ** 2).mean()))
+        rec = {"mom_rms_ref": ref_rms, "mom_rms_mean": float(np.mean(rms)), "mom_rms_seeds": [float(x) for x in rms],
+               "mom_rms_over_ref": float(np.mean(rms) / ref_rms), "mass": cfg.mass}
+        if method == "p3m":
+            if a.backend == "gpu":
+                pr = PS.concept_powerspec(d["pos_p3m"], L, n, interlace=bool(a.estimator_interlace)).power
+            else:
+                from oracle import concept_ps
+                geom = PS.bin_geometry(n)
+                rg = [(int(f), int(l)) for f, l in zip(geom.first_k2, list(geom.first_k2[1:] - 1) + [geom.k2_end - 1])]
+                pr = concept_ps.powerspec(d["pos_p3m"], L, n, rg, interlace=bool(a.estimator_interlace))[1]
+            rec["P_of_reference_snapshot"] = pr.tolist()
+            rec["P_mean"] = np.mean(P, 0).tolist()
+            rec["P_over_reference_snapshot"] = (np.mean(P, 0) / pr).tolist()
+            rec["modes"] = PS.bin_geometry(n).modes.tolist()
+        out[method] = rec
+        print(f"giant32 {method}: mom rms {np.mean(rms):.1f} (ref {ref_rms:.1f}, ratio {np.mean(rms) / ref_rms:.3f})"
+              + (f", P / P(reference snapshot): {np.array2string(np.array(rec['P_over_reference_snapshot']), precision=2)}"
+                 if method == "p3m" else ""), flush=True)
+    return out
+
+
 # ------------------------------------------------------------------------------------ driver
 def main(argv=None):
     ap = argparse.ArgumentParser()
@@ -205,8 +249,9 @@ def main(argv=None):
     ap.add_argument("--softening", type=float, default=None, help="Plummer ε in units of L/cbrt(N)")
     ap.add_argument("--eta", type=float, default=0.025, help="accuracy parameter of the sub-step criterion")
     ap.add_argument("--max-sub", type=int, default=32, help="largest number of short-range sub-steps per base step; 1: off")
-    ap.add_argument("--lattice-offset", type=float, default=0.5, help="IC lattice offset in particle spacings")
+    ap.add_argument("--lattice-offset", type=float, default=0.0, help="IC lattice offset in particle spacings")
     ap.add_argument("--estimator-interlace", type=int, default=1, help="0: estimator without interlacing")
+    ap.add_argument("--deconv-order", type=int, default=None, help="powers of the CIC window divided out of the mesh force")
     ap.add_argument("--out", default=None)
     a = ap.parse_args(argv)
     cosmo = Cosmology()
@@ -215,6 +260,9 @@ def main(argv=None):
               "lattice_offset": a.lattice_offset, "eta": a.eta, "max_sub": a.max_sub, "estimator_interlace": bool(a.estimator_interlace), "runs": {}}
     spectra = {}
     for meth in a.methods.split(","):
+        if meth == "giant32":
+            report["giant32"] = giant32(a, cosmo, run)
+            continue
         if meth == "snapvspk":
             method, L, tags, outs = "pm", 1000.0, ["SnapVsPK_a=0.17", "SnapVsPK_a=1.00"], [1.0 / 6.0, 1.0]
         else:
@@ -222,6 +270,8 @@ def main(argv=None):
         refs = [PS.read_powerspec(os.path.join(GOLD, t + ".txt")) for t in tags]
         lin = TabulatedLinear(cosmo, refs[-1], L, a_file=1.0)
         cfg = force_cfg(method, a.n, L, cosmo)
+        if a.deconv_order is not None:
+            cfg.deconvolve = (a.deconv_order >= 1, a.deconv_order >= 2)
         if a.softening is not None:
             cfg.softening_frac = a.softening
         acc = {round(o, 6): [] for o in outs}
