@@ -1,0 +1,167 @@
+"""Parity at the sizes BASELINE.json names: the small parity cases of
+test_gpu_force.py / test_gpu_density.py are repeated where the kernels run their production
+configurations.
+
+  C1  64³ particles / 64³ mesh, the whole `CiC/3D startbetingelser1.py` pipeline (:62-231, 274-318):
+      GRF -> ψ -> displaced lattice -> CIC deposit -> both P(k)s, against the float64 restatement
+  C3  PP at 128³: 4 096 random i-particles against all 2 097 152 j vs the C oracle
+  C4  PM at 256³ / 512³: the whole acceleration field vs the C / scipy oracle (≈20 s of host time)
+  C4' P³M at 128³ / 256³ in full vs the C oracle (the mesh + short-range composition at a size the
+      oracle finishes in seconds)
+  C5  P³M at 512³ / 1024³: short range of ≥ 10⁴ particles of a spatial subset vs the C oracle on a
+      cut-out box; total force of 2 048 random particles vs the direct periodic (Ewald) sum over all
+      134 M particles on the device — the one check of the 1024³ mesh force that does not go through
+      a CPU FFT of that size.
+Tolerances: 1e-5 (max |Δ| / rms) wherever the oracle computes the same quantity; the C5 Ewald check
+compares P³M with the exact periodic force, i.e. it measures the P³M method error (stated there).
+"""
+import numpy as np
+import pytest
+
+from conftest import surrogate_pk, zeldovich_particles
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def _err(a, ref):
+    return np.abs(a - ref).max() / np.sqrt((ref ** 2).mean())
+
+
+def test_c1_cic_script_end_to_end_64():
+    """Config 1 end to end: same draws, same surrogate P(k) on the k grid of the script."""
+    from nbody_b200 import api
+    from oracle import restate
+    n, L = 64, 1000.0
+    rs = np.random.RandomState(20250611)
+    c1 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    c2 = rs.normal(0, 1 / np.sqrt(2), size=(n, n, n))
+    km = restate.k_mag_grid(n, L)
+    km[0, 0, 0] = 1e-10
+    pk = surrogate_pk(km)
+    # reference-side (float64 restatement of the script)
+    R = restate.hermitian_R(c1, c2, guard=True)
+    d_ref, psi_ref = restate.grf_delta_psi(pk, R, L, n)
+    pos_ref = (restate.lattice(L, n) + np.column_stack([p.ravel() for p in psi_ref])) % L
+    grid_ref = restate.cic_density(pos_ref, L, n) - 1.0
+    # device side through the reference-named entry points
+    d_x, psi = api.grf_delta_psi(pk, L, n, c1=c1, c2=c2, guard=True, precision="f64")
+    assert np.abs(d_x - d_ref).max() <= 1e-10 * np.abs(d_ref).max()
+    d_cic, pos = api.particle_assigment(psi, L, n, precision="f64", return_particles=True)
+    dpos = np.abs(pos - pos_ref)
+    assert np.minimum(dpos, L - dpos).max() <= 1e-9 * L
+    assert np.abs(d_cic - grid_ref).max() <= 1e-9 * np.abs(grid_ref).max()
+    idx = api.cic_density(pos_ref, L, n, return_index=True)[1]
+    assert np.array_equal(idx, restate.cic_index_weight(pos_ref, L, n)[0])          # bit-exact cell indices
+    for field, fromcic in ((d_ref, False), (grid_ref, True)):
+        k, p, c = api.compute_power_spectrum(field, fromcic, L=L, N=n, withfac=True, variant="cic3d", return_counts=True)
+        kr, pr, cr = restate.compute_power_spectrum(field, fromcic, L, n, withfac=True, variant="cic3d", return_counts=True)
+        assert np.array_equal(c, cr) and np.array_equal(k, kr)                      # bin counts bit-exact
+        assert np.abs(p / pr - 1).max() <= TOL
+
+
+def test_c3_pp_128_random_i_subset_against_all_j():
+    from nbody_b200.engine import default_engine
+    from oracle import cport
+    n, L = 128, 500.0
+    pos = zeldovich_particles(n, L, seed=7)
+    rs = np.random.RandomState(3)
+    perm = rs.permutation(pos.shape[0])
+    pos = np.ascontiguousarray(pos[perm])                       # the first 4096 rows are a random subset
+    ni, eps = 4096, 0.025 * L / n
+    eng = default_engine()
+    half = 0.5 * L
+    p4 = eng.pp_pack(eng.to_device(pos), origin=(half, half, half), mass=1.0)
+    acc = eng.pp_accel(p4[:ni].contiguous(), p4, eps, scale=1.0).cpu().numpy()
+    ref = cport.pp_accel(pos, 1.0, 1.0, eps, 0.0, 0, ni)
+    err = _err(acc, ref)
+    print(f"C3 PP 128^3, {ni} i x {pos.shape[0]} j: err {err:.2e}")
+    assert err <= TOL
+
+
+def test_c4_pm_256_512_full_field_against_the_c_oracle():
+    from nbody_b200 import force as F
+    from nbody_b200.engine import default_engine
+    from nbody_b200.params import ForceConfig
+    from oracle import cpu_step
+    n, N, L = 256, 512, 1000.0
+    pos = zeldovich_particles(n, L, seed=5)
+    cfg = ForceConfig(method="pm", npart=n ** 3, boxsize=L, gridsize=N, interlace=(True, True), deconvolve=(True, True),
+                      G=1.0, mass=1.0)
+    eng = default_engine()
+    acc = F.ForceStepper(cfg, eng).accel(eng.to_device(pos)).cpu().numpy()
+    ref = cpu_step.pm_accel(cfg, pos)
+    err = _err(acc, ref)
+    print(f"C4 PM 256^3/512^3 full field: err {err:.2e}")
+    assert err <= TOL
+
+
+def test_p3m_128_256_full_against_the_c_oracle():
+    from nbody_b200 import force as F
+    from nbody_b200.engine import default_engine
+    from nbody_b200.params import ForceConfig
+    from oracle import cpu_step
+    n, N, L = 128, 256, 1000.0
+    pos = zeldovich_particles(n, L, seed=11)
+    cfg = ForceConfig(method="p3m", npart=n ** 3, boxsize=L, gridsize=N, interlace=(True, True),
+                      deconvolve=(True, True), G=1.0, mass=1.0)
+    eng = default_engine()
+    acc = F.ForceStepper(cfg, eng).accel(eng.to_device(pos)).cpu().numpy()
+    ref = cpu_step.accel(cfg, pos)
+    err = _err(acc, ref)
+    print(f"P3M 128^3/256^3 full: err {err:.2e}")
+    assert err <= TOL
+
+
+def test_c5_p3m_512_1024_subset_and_ewald_checks():
+    import torch
+    import bench
+    from nbody_b200 import force as F
+    from nbody_b200.engine import default_engine
+    from nbody_b200.params import ForceConfig
+    from oracle import cport
+    eng = default_engine()
+    n, N, L = 512, 1024, 1000.0
+    pos = bench.zeldovich_on_device(eng, n, L, seed=20250611)            # the bench's config-5 particle set
+    cfg = ForceConfig(method="p3m", npart=n ** 3, boxsize=L, gridsize=N, interlace=(True, True),
+                      deconvolve=(True, True), G=1.0, mass=1.0)
+    st = F.ForceStepper(cfg, eng)
+    acc_s = torch.full_like(pos, float("nan"))
+    st.short_range(pos, acc_s, accumulate=False)
+    assert bool(torch.isfinite(acc_s).all()), "a particle was left unwritten or picked up a NaN"
+    tot = acc_s.sum(dim=0).abs().max().item()
+    assert tot <= 1e-4 * acc_s.abs().sum(dim=0).max().item()             # pair forces cancel
+    rms_s = float(torch.sqrt((acc_s ** 2).mean()).item())
+    # (1) short range of every particle of a (2 x 21 Mpc)^3 cube (and of one across the box corner) vs the C oracle
+    #     on the cut-out that holds all their partners
+    for centre, half in ((torch.tensor([500.0, 480.0, 505.0]), 21.0), (torch.zeros(3), 12.0)):
+        rel = (pos - centre.to(pos) + 0.5 * L) % L - 0.5 * L
+        dist = rel.abs().max(dim=1).values
+        j_glob = torch.nonzero(dist < half + cfg.r_cut * 1.0001).squeeze(1)
+        sub = rel[j_glob].cpu().numpy()
+        inner = (np.abs(sub).max(axis=1) < half)
+        ref = cport.p3m_short_accel(np.ascontiguousarray(sub + 2.0 * L), 4.0 * L, cfg.r_s, cfg.r_cut, cfg.G, cfg.mass,
+                                    cfg.eps)[inner]
+        got = acc_s[j_glob].cpu().numpy()[inner]
+        err = np.abs(got - ref).max() / max(rms_s, np.sqrt((ref ** 2).mean()))
+        print(f"C5 short range: centre {centre.tolist()} n_i {int(inner.sum())} of {sub.shape[0]} err {err:.2e}")
+        assert inner.sum() >= (10000 if half > 20 else 1000)
+        assert err <= TOL
+    del acc_s, rel, dist
+    # (2) total P3M force (1024^3 mesh chain + short range) of 2048 random particles vs the direct periodic sum
+    #     over all 134 M particles (nearest image + Ewald table, itself checked against the float64 Ewald sum in
+    #     test_gpu_ewald.py).  This is the P3M METHOD error (Gaussian split at r_s = 1.25 cells cut at 4.5 r_s,
+    #     CIC mesh), not a rounding error: a few 1e-3 of the rms force.
+    acc = st.accel(pos)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    idx = torch.randint(0, pos.shape[0], (2048,), generator=g, device=pos.device)
+    got = acc[idx].cpu().numpy()
+    rms = float(torch.sqrt((acc ** 2).mean()).item())
+    half = 0.5 * L
+    p4 = eng.pp_pack(pos, origin=(half, half, half), mass=1.0)
+    exact = eng.pp_accel_ewald(p4[idx].contiguous(), p4, cfg.eps, L, eng.ewald_table(L, 64), 64,
+                               scale=cfg.G * cfg.mass).cpu().numpy()
+    d = got - exact
+    rel_rms, rel_max = np.sqrt((d ** 2).mean()) / rms, np.abs(d).max() / rms
+    print(f"C5 P3M total vs direct Ewald sum over {pos.shape[0]} particles: rms {rel_rms:.2e} max {rel_max:.2e} of the rms force")
+    assert rel_rms < 1e-2 and rel_max < 1e-1
