@@ -227,6 +227,17 @@ int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy,
 int nb_pp_accel(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void* jpos_xyzw, int64_t nj,
                 double eps, double box, double scale, int variant, int accumulate, double* acc,
                 void* stream);
+/* Near-field fix of nb_pp_accel's float32 coordinates for i == j sets (pos is the (np,3) float64 array that
+ * nb_pp_pack packed with origin (ox,oy,oz) and uniform weight mass_w; perm / cell_start from nb_cell_sort of
+ * the same positions on a box of side L with ncs >= 3 cells of side >= r_c): for every pair with r < r_c
+ * adds scale x (float64 pair term - the float32 term nb_pp_accel summed for that pair) to acc, for the
+ * i-particles [i0, i0 + ni) of pos (acc has ni rows: an i-sharded rank passes its own range).  periodic = 1
+ * for the minimum-image variant (box = L), 0 for open boundaries.  Restores max|dg|/rms|g| <= 1e-5 where a
+ * single pair closer than the softening length would otherwise leave 4e-4 (128^3, L = 500). */
+int nb_pp_near_fix(nb_ctx* ctx, const double* pos, int64_t np, int64_t i0, int64_t ni, const int32_t* perm,
+                   const int32_t* cell_start,
+                   int ncs, double L, double ox, double oy, double oz, double mass_w, double eps, double r_c,
+                   int periodic, double scale, double* acc, void* stream);
 
 /* ---- K4e  periodic PP with Ewald summation ----------------------------------
  * No reference source (CONCEPT PP gravity in a periodic box: softened nearest-image force plus a

@@ -180,6 +180,107 @@ pp_accel_kernel(const float4* __restrict__ ipos, int64_t ni, const float4* __res
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Near-field fix of the FP32 coordinates.  nb_pp_pack rounds x - origin to float32: 24 bits over the box
+// (1.5e-5 Mpc at |x| = 250 Mpc).  For a pair closer than a few softening lengths that is 1e-4 of its
+// separation, and ONE such pair puts the particle's acceleration 4e-4 (of the rms) off the float64 sum
+// at 128^3 (median 1.6e-7, 99th percentile 1.7e-5: measured, tests/test_gpu_baseline_sizes.py).
+// Instead of paying two FP32 words per coordinate for all Np^2 pairs, the few pairs with r < r_c are
+// visited once more through a cell list (nb_cell_sort): the float64 pair term minus the term the
+// all-pairs kernel added for the same pair — replayed with the same float32 operations, rsqrt.approx
+// included — is summed in float64 and added to acc.  ~0.5 pairs per particle at r_c = 20 eps.
+template <bool PERIODIC>
+__global__ void __launch_bounds__(256)
+pp_near_fix_kernel(const double* __restrict__ pos, int64_t i0, int64_t ni, const int* __restrict__ perm,
+                   const int* __restrict__ cell_start, int ncs, double L, double inv_cs, double ox, double oy,
+                   double oz, float w, double eps2, double rc2, double scale, double* __restrict__ acc) {
+  const float eps2f = (float)eps2, boxf = (float)L, inv_boxf = 1.f / (float)L;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = i0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < i0 + ni; i += stride) {
+    const double xi = pos[3 * i], yi = pos[3 * i + 1], zi = pos[3 * i + 2];
+    int ci[3];
+    {
+      const double v[3] = {xi, yi, zi};
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        double xw = v[a];
+        if (xw < 0.0 || xw >= L) xw = nb_pymod(xw, L);
+        int c = (int)(xw * inv_cs);
+        ci[a] = c >= ncs ? ncs - 1 : (c < 0 ? 0 : c);
+      }
+    }
+    const float nxi = -(float)(xi - ox), nyi = -(float)(yi - oy), nzi = -(float)(zi - oz);
+    double sx = 0.0, sy = 0.0, sz = 0.0;
+    for (int dxc = -1; dxc <= 1; ++dxc)
+      for (int dyc = -1; dyc <= 1; ++dyc)
+        for (int dzc = -1; dzc <= 1; ++dzc) {
+          int cx = ci[0] + dxc, cy = ci[1] + dyc, cz = ci[2] + dzc;
+          if (PERIODIC) {
+            cx = (cx + ncs) % ncs; cy = (cy + ncs) % ncs; cz = (cz + ncs) % ncs;
+          } else if (cx < 0 || cy < 0 || cz < 0 || cx >= ncs || cy >= ncs || cz >= ncs) {
+            continue;
+          }
+          const int c = (cx * ncs + cy) * ncs + cz;
+          for (int s = cell_start[c], e = cell_start[c + 1]; s < e; ++s) {
+            const int64_t j = perm[s];
+            if (j == i) continue;
+            const double xj = pos[3 * j], yj = pos[3 * j + 1], zj = pos[3 * j + 2];
+            double dx = xj - xi, dy = yj - yi, dz = zj - zi;
+            if (PERIODIC) {
+              dx -= L * rint(dx / L); dy -= L * rint(dy / L); dz -= L * rint(dz / L);
+            }
+            const double r2 = dx * dx + dy * dy + dz * dz;
+            if (r2 >= rc2) continue;
+            // float64 pair term
+            const double q2 = r2 + eps2;
+            const double inv = q2 > 0.0 ? 1.0 / sqrt(q2) : 0.0;
+            const double fp = (double)w * inv * inv * inv;
+            // the term pp_accel_kernel added for this pair (same operations, same rounding)
+            float fx = (float)(xj - ox) + nxi, fy = (float)(yj - oy) + nyi, fz = (float)(zj - oz) + nzi;
+            if (PERIODIC) {
+              fx = fmaf(-boxf, rintf(fx * inv_boxf), fx);
+              fy = fmaf(-boxf, rintf(fy * inv_boxf), fy);
+              fz = fmaf(-boxf, rintf(fz * inv_boxf), fz);
+            }
+            float r2f = fmaf(fx, fx, eps2f);
+            r2f = fmaf(fy, fy, r2f);
+            r2f = fmaf(fz, fz, r2f);
+            const float rinv = rsqrt_approx(r2f);
+            float sf = (w * rinv) * (rinv * rinv);
+            if (!(r2f > 0.f)) sf = 0.f;
+            sx += fp * dx - (double)sf * (double)fx;
+            sy += fp * dy - (double)sf * (double)fy;
+            sz += fp * dz - (double)sf * (double)fz;
+          }
+        }
+    acc[3 * (i - i0) + 0] += sx * scale;
+    acc[3 * (i - i0) + 1] += sy * scale;
+    acc[3 * (i - i0) + 2] += sz * scale;
+  }
+}
+
+extern "C" int nb_pp_near_fix(nb_ctx* ctx, const double* pos, int64_t np, int64_t i0, int64_t ni, const int32_t* perm,
+                              const int32_t* cell_start, int ncs, double L, double ox, double oy, double oz,
+                              double mass_w, double eps, double r_c, int periodic, double scale, double* acc,
+                              void* stream) {
+  NB_REQUIRE(ctx, "ctx is NULL");
+  if (np == 0 || ni == 0) return NB_OK;
+  NB_REQUIRE(pos && perm && cell_start && acc, "NULL argument");
+  NB_REQUIRE(i0 >= 0 && ni >= 0 && i0 + ni <= np, "bad i range");
+  NB_REQUIRE(ncs >= 3 && L > 0 && r_c > 0 && L / ncs >= r_c && eps >= 0, "cells must be at least r_c wide, ncs >= 3");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  const int nblk = nb_grid_for(ctx, ni, 256, 16);
+  if (periodic)
+    pp_near_fix_kernel<true><<<nblk, 256, 0, st>>>(pos, i0, ni, perm, cell_start, ncs, L, (double)ncs / L, ox, oy, oz,
+                                                   (float)mass_w, eps * eps, r_c * r_c, scale, acc);
+  else
+    pp_near_fix_kernel<false><<<nblk, 256, 0, st>>>(pos, i0, ni, perm, cell_start, ncs, L, (double)ncs / L, ox, oy, oz,
+                                                    (float)mass_w, eps * eps, r_c * r_c, scale, acc);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
 extern "C" int nb_pp_pack(nb_ctx* ctx, const double* pos, int64_t np, double ox, double oy, double oz,
                           double mass, const double* masses, void* out_xyzw, void* stream) {
   NB_REQUIRE(ctx, "ctx is NULL");

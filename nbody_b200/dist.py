@@ -483,6 +483,18 @@ class DistForceStepper:
         mk("all_gather_j", lambda: self.comm.all_gather(allj, mine))
         mk("pp_accel", lambda: self.eng.pp_accel(mine[:pos.shape[0]], allj, c.eps,
                                                  box=c.boxsize if periodic else 0.0, scale=c.G * c.mass, out=acc))
+        if c.eps > 0 and int(c.boxsize / (20.0 * c.eps)) >= 3:
+            # float64 near-field fix (force.ForceStepper.pp): needs the float64 positions of all j — the ranks
+            # hold contiguous index ranges, so the gathered array is the full set with padding at its very end
+            def fix():
+                minep = torch.zeros((chunk, 3), dtype=torch.float64, device=self.eng.device)
+                minep[:pos.shape[0]].copy_(pos)
+                allp = torch.empty((self.world * chunk, 3), dtype=torch.float64, device=self.eng.device)
+                self.comm.all_gather(allp, minep)
+                self.eng.pp_near_fix(allp[:n_total], c.boxsize, c.eps, 20.0 * c.eps, (half, half, half), acc,
+                                     periodic=bool(periodic), scale=c.G * c.mass, mass=1.0, i0=self.rank * chunk,
+                                     ni=pos.shape[0])
+            mk("pp_near_fix", fix)
         return acc
 
     # -- migration ----------------------------------------------------------------------------------

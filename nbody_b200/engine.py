@@ -375,6 +375,23 @@ class Engine:
                                         int(bool(accumulate)), _ptr(out), self.stream), "nb_pp_accel")
         return out
 
+    def pp_near_fix(self, pos: torch.Tensor, L: float, eps: float, r_c: float, origin, acc: torch.Tensor,
+                    periodic: bool = False, scale: float = 1.0, mass: float = 1.0, max_cells: int = 256,
+                    i0: int = 0, ni: int | None = None):
+        """Adds the float64 - float32 difference of every pair closer than r_c to `acc` (nb_pp_near_fix; the
+        all-pairs kernel keeps 24-bit coordinates).  No-op when the box holds fewer than 3 cells of side r_c."""
+        self._check_pos(pos)
+        ncs = min(int(L / r_c), int(max_cells))
+        if ncs < 3 or pos.shape[0] == 0:
+            return acc
+        _s4, perm, cell_start = self.cell_sort(pos, L, ncs, mass=mass)
+        ni = pos.shape[0] - int(i0) if ni is None else int(ni)
+        _lib.check(self.lib.nb_pp_near_fix(self.ctx, _ptr(pos), pos.shape[0], int(i0), ni, _ptr(perm), _ptr(cell_start), ncs,
+                                           float(L), float(origin[0]), float(origin[1]), float(origin[2]), float(mass),
+                                           float(eps), float(r_c), int(bool(periodic)), float(scale), _ptr(acc),
+                                           self.stream), "nb_pp_near_fix")
+        return acc
+
     # -- K4e: periodic PP with Ewald summation ------------------------------------------
     def ewald_table(self, box: float, g: int = 64, alpha_box: float = 2.0, nreal: int = 4, nfour: int = 5,
                     want_f64: bool = False):

@@ -29,6 +29,7 @@ class ForceStepper:
         self.cfg = cfg
         self.eng = engine or default_engine()
         self.pp_variant = pp_variant
+        self.pp_near_fix = True
         self._force = None
         self._force_s = None
         self._acc = None
@@ -98,6 +99,10 @@ class ForceStepper:
             return acc
         self.eng.pp_accel(p4, p4, c.eps, box=c.boxsize if periodic else 0.0, scale=c.G * c.mass,
                           variant=self.pp_variant, out=acc)
+        if self.pp_near_fix and c.eps > 0:
+            # pairs closer than 20 softening lengths once more in float64 (the packed coordinates keep 24 bits)
+            self.eng.pp_near_fix(pos, c.boxsize, c.eps, 20.0 * c.eps, (half, half, half), acc, periodic=bool(periodic),
+                                 scale=c.G * c.mass, mass=1.0)
         return acc
 
     def _tail_to_host(self, tail, pos, mom, out_pos, out_mom, chunks=8):
