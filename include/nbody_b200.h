@@ -168,6 +168,12 @@ int nb_hermitian_R(nb_ctx* ctx, const double* c1, const double* c2, int N, int g
 int nb_grf_synthesize(nb_ctx* ctx, const double* pk_grid, const double* c1, const double* c2, int N,
                       const double* k_vals, double fac, int guard_selfconj, int prec,
                       void* delta_out, void* psi_out, void* stream);
+/* Second-order (2LPT) displacement psi2 = grad(phi2), laplace(phi2) = sum_{a>b} [phi1,aa phi1,bb - phi1,ab^2],
+ * laplace(phi1) = delta, of the lattice ICs (`realization_options['LPT'] = 2`, Different_Sizes/Giant.param:70-72;
+ * the reference looks at both orders in 1LPTvs2LPT/1vs2tlptplotter.py).  float64: delta (N,N,N) in, work6 = 6 N^3
+ * doubles of scratch, psi2_out (3,N,N,N).  11 cuFFT transforms + the spectral-factor and source kernels. */
+int nb_lpt2_displacement(nb_ctx* ctx, const double* delta, int N, const double* k_vals, double* work6,
+                         double* psi2_out, void* stream);
 
 /* ---- K3  CIC gather, displacement, kick / drift -----------------------------------------
  * nb_cic_gather: out[p,c] (=|+=) scale · Σ_8 w · field[c][cell]  with the deposit's float64
@@ -335,6 +341,19 @@ int nb_snapshot_delta_batch(nb_ctx* ctx, const double* pos, const int64_t* offse
                             int64_t total_particles, int B, const double* cell_dev, int N,
                             const double* sinc_tabs_dev, int guard, const int32_t* submean_dev,
                             void* grids, int prec, void* stream);
+/* Batched snapshot P(k) (replaces `mp.Pool(10).starmap(compute_power_spectrum_from_snapshot, ...)`,
+ * Different_Sizes/Plotter.py:205-238, and the per-file loops of SnapVsPK/Power_compare.py:211-235): B particle
+ * sets that share the mesh size N are deposited, turned into overdensities grid / (Np_b / N^3) - 1, transformed by
+ * one batched R2C and binned like nb_power_spectrum, per snapshot b with its own tables: cell_dev[b],
+ * npart_dev[b] (device doubles), k2_tabs_dev / sinc_tabs_dev [B][N], thresh_dev [B][n_edges] (device),
+ * thresh_first/_last/_hi_host[b] and norm_host[b] (HOST doubles).  counts [B][n_edges-1] int64 and sums
+ * [B][n_edges-1] float64 (device) are zeroed then filled.  float32 grids. */
+int nb_snapshot_pk_batch(nb_ctx* ctx, const double* pos, const int64_t* offsets_dev, int64_t total_particles, int B,
+                         const double* cell_dev, const double* npart_dev, int N, const double* k2_tabs_dev,
+                         const double* sinc_tabs_dev, const double* thresh_dev, const double* thresh_first_host,
+                         const double* thresh_last_host, const double* thresh_hi_host, int n_edges, int window_power,
+                         int clip_mode, double clip_val, const double* norm_host, int closed_last, int64_t* counts,
+                         double* sums, void* stream);
 
 #ifdef __cplusplus
 }

@@ -37,6 +37,7 @@ PROTOTYPES = {
                                              c_i32, c_i32, c_i32, c_f64, c_f64, c_i32, c_vp, c_vp, c_vp]),
     "nb_hermitian_R": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp]),
     "nb_grf_synthesize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_f64, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "nb_lpt2_displacement": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "nb_cic_gather": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_vp, c_vp]),
     "nb_displace_wrap": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_f64, c_vp]),
     "nb_kick_drift": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_f64, c_f64, c_f64, c_vp]),
@@ -72,6 +73,8 @@ PROTOTYPES = {
     "nb_grid_add": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp]),
     "nb_snapshot_delta_batch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_i32,
                                         c_vp]),
+    "nb_snapshot_pk_batch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                     c_i32, c_i32, c_i32, c_f64, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "nb_ewald_table": (c_i32, [c_vp, c_f64, c_i32, c_f64, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "nb_pp_accel_ewald": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64, c_vp, c_i32, c_i32, c_vp, c_vp]),
 }

@@ -200,6 +200,65 @@ def compute_power_spectrum_from_snapshot(snapshot_path, L, Nmesh, deconvolve=Fal
     return power_spectrum_from_positions(pos, L, Nmesh, deconvolve, use_fac, variant, precision)
 
 
+def power_spectra_from_positions(positions_list, boxsizes, Nmesh, variant="plotter"):
+    """Batched form of power_spectrum_from_positions for snapshots that share the mesh size (one library
+    call, nb_snapshot_pk_batch): returns [(k_centers[valid], Pk[valid])] in input order.
+    variant "plotter" = Different_Sizes/Plotter.py:148-202 (W clipped at 1e-3, δ_k / W), "lpt" =
+    1LPTvs2LPT/1vs2tlptplotter.py:81-116 (100 edges), "power_compare" = Power_compare.py:135-200 with
+    deconvolve=False, use_fac=False."""
+    eng = default_engine()
+    plist = [_positions(p) for p in positions_list]
+    B = len(plist)
+    if B == 0:
+        return []
+    Nmesh = int(Nmesh)
+    offsets = np.concatenate([[0], np.cumsum([p.shape[0] for p in plist])]).astype(np.int64)
+    boxes = np.broadcast_to(np.asarray(boxsizes, dtype=np.float64), (B,)).copy()
+    pos = eng.to_device(np.concatenate(plist))
+    if variant in ("plotter", "lpt"):
+        kw = dict(n_edges=300 if variant == "plotter" else 100, window_power=2, clip_mode=2, clip_val=1e-3,
+                  kq_form="piN_L")
+    elif variant == "power_compare":
+        kw = dict(n_edges=300)
+    else:
+        raise ValueError(f"unknown variant {variant!r}")
+    edges, counts, sums = eng.snapshot_pk_batch(pos, offsets, boxes, Nmesh, closed_last=True, **kw)
+    counts, sums = counts.cpu().numpy(), sums.cpu().numpy()
+    out = []
+    for b in range(B):
+        centers = 0.5 * (edges[b][:-1] + edges[b][1:])
+        v = counts[b] > 0
+        out.append((centers[v], sums[b][v] / counts[b][v]))
+    return out
+
+
+def power_spectra_of_runs(root_dir, pattern="3giant*", variant="plotter"):
+    """The main block of Different_Sizes/Plotter.py:205-242 without the process pool: every run directory
+    `<root>/3giant<N>(pm|p3m)` contributes its first snapshot, mesh size = N of the directory name, boxsize from
+    the snapshot's attributes; runs that share a mesh size go through ONE batched call.  Returns
+    [((method, N_in, ngrid, boxsize), (k, Pk))] sorted by N_in like the reference's `plot_data`."""
+    import glob
+    import os
+    import re
+    from . import snapshot
+    jobs = []
+    for run in sorted(glob.glob(os.path.join(root_dir, pattern))):
+        snaps = sorted(snapshot.find_hdf5_files(run))
+        m = re.search(r"giant(\d+)(p3m|pm)", run)
+        if not snaps or not m:
+            continue
+        n_in = int(m.group(1))
+        jobs.append(((m.group(2), n_in, n_in, float(snapshot.read_boxsize(snaps[0]))), snaps[0]))
+    results = [None] * len(jobs)
+    for ngrid in sorted({j[0][2] for j in jobs}):
+        idx = [i for i, j in enumerate(jobs) if j[0][2] == ngrid]
+        pos = [snapshot.read_positions(jobs[i][1]) for i in idx]
+        for i, r in zip(idx, power_spectra_from_positions(pos, [jobs[i][0][3] for i in idx], ngrid, variant)):
+            results[i] = r
+    data = sorted(zip([j[0] for j in jobs], results), key=lambda x: x[0][1])
+    return data
+
+
 # --------------------------------------------------------------------------------- a5
 def compute_power_spectrum(delta_x, fromcic=False, kx=0, ky=0, kz=0, L=0, N=0, withfac=False,
                            variant="power_compare", precision="f32", return_counts=False):

@@ -187,3 +187,77 @@ extern "C" int nb_snapshot_delta_batch(nb_ctx* ctx, const double* pos, const int
   return batch_run<float, float2>(ctx, pos, offsets_dev, total_particles, B, cell_dev, N, sinc_tabs_dev, guard,
                                   submean_dev, (float*)grids, CUFFT_R2C, CUFFT_C2R, st);
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Batched snapshot P(k): replaces the process pool of Different_Sizes/Plotter.py:205-238
+// (`mp.Pool(10).starmap(compute_power_spectrum_from_snapshot, arg_list)`, one snapshot per worker) and the
+// per-file loops of SnapVsPK/Power_compare.py:211-235 for snapshots that share a mesh size: B particle sets
+// are deposited into [B][N][N][N] by one kernel, turned into overdensities (grid / (Np_b / N³) - 1,
+// Plotter.py:172-173 = Power_compare.py:153-157), transformed by ONE batched cuFFT call and binned by the K6
+// kernel once per snapshot, all on the caller's stream without a host round trip in between.
+__global__ void __launch_bounds__(256)
+batch_overdensity_kernel(float* __restrict__ grids, int64_t n3, const double* __restrict__ npart) {
+  const int b = blockIdx.y;
+  const double inv_mean = (double)n3 / npart[b];
+  float* g = grids + (int64_t)b * n3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n3; i += (int64_t)gridDim.x * blockDim.x)
+    g[i] = (float)((double)g[i] * inv_mean - 1.0);
+}
+
+int nb_pk_bin_spectrum(nb_ctx* ctx, const void* spec, int N, int y0, int nyl, int prec, const double* k2_tab,
+                       const double* sinc_tab, const double* thresh, double thresh_hi, int n_edges,
+                       int window_power, int clip_mode, double clip_val, double norm, int closed_last,
+                       double k2min_host, double k2max_host, int64_t* counts, double* sums, cudaStream_t st);
+
+extern "C" int nb_snapshot_pk_batch(nb_ctx* ctx, const double* pos, const int64_t* offsets_dev,
+                                    int64_t total_particles, int B, const double* cell_dev,
+                                    const double* npart_dev, int N, const double* k2_tabs_dev,
+                                    const double* sinc_tabs_dev, const double* thresh_dev,
+                                    const double* thresh_first_host, const double* thresh_last_host,
+                                    const double* thresh_hi_host, int n_edges, int window_power, int clip_mode,
+                                    double clip_val, const double* norm_host, int closed_last, int64_t* counts,
+                                    double* sums, void* stream) {
+  NB_REQUIRE(ctx && offsets_dev && cell_dev && npart_dev && k2_tabs_dev && sinc_tabs_dev && thresh_dev &&
+                 thresh_first_host && thresh_last_host && thresh_hi_host && norm_host && counts && sums,
+             "NULL argument");
+  NB_REQUIRE(B >= 1 && B <= 65535, "batch size must be in [1, 65535]");
+  NB_REQUIRE(N >= 2 && n_edges >= 2 && (int64_t)N * N * N * B < ((int64_t)1 << 36), "bad mesh size / n_edges");
+  NB_REQUIRE(total_particles >= 0 && (total_particles == 0 || pos), "pos is NULL");
+  NB_REQUIRE(window_power >= 0 && window_power <= 2 && clip_mode >= 0 && clip_mode <= 2, "bad window options");
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n3 = (int64_t)N * N * N, nspec = (int64_t)N * N * (N / 2 + 1);
+  void *grids_v = nullptr, *spec = nullptr;
+  int rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_REAL0, sizeof(float) * (size_t)n3 * B, &grids_v))) return rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_SPEC0, sizeof(float2) * (size_t)nspec * B, &spec))) return rc;
+  float* grids = (float*)grids_v;
+  NB_CHECK_CUDA(cudaMemsetAsync(grids, 0, sizeof(float) * (size_t)n3 * B, st));
+  NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * (size_t)(n_edges - 1) * B, st));
+  NB_CHECK_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * (size_t)(n_edges - 1) * B, st));
+  if (total_particles > 0) {
+    batch_deposit_kernel<float><<<nb_grid_for(ctx, total_particles, 256, 16), 256, 0, st>>>(pos, offsets_dev, B,
+                                                                                         cell_dev, N, grids);
+    NB_LAUNCHED(ctx);
+  }
+  int chunks = (int)((n3 + 256 * 8 - 1) / (256 * 8));
+  const int max_chunks = (ctx->num_sms * 8 + B - 1) / B;
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  batch_overdensity_kernel<<<dim3(chunks, B), 256, 0, st>>>(grids, n3, npart_dev);
+  NB_LAUNCHED(ctx);
+  int dims[3] = {N, N, N};
+  cufftHandle fwd;
+  if ((rc = nb_plan_many(ctx, 3, dims, B, CUFFT_R2C, 7001, nullptr, 1, 0, nullptr, 1, 0, st, &fwd))) return rc;
+  NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)grids, (cufftComplex*)spec));
+  for (int b = 0; b < B; ++b) {
+    NB_REQUIRE(thresh_first_host[b] > 0 && thresh_last_host[b] > thresh_first_host[b], "bad bin thresholds");
+    if ((rc = nb_pk_bin_spectrum(ctx, (const float2*)spec + (int64_t)b * nspec, N, 0, N, NB_F32,
+                                 k2_tabs_dev + (int64_t)b * N, sinc_tabs_dev + (int64_t)b * N,
+                                 thresh_dev + (int64_t)b * n_edges, thresh_hi_host[b], n_edges, window_power, clip_mode,
+                                 clip_val, norm_host[b], closed_last, thresh_first_host[b], thresh_last_host[b],
+                                 counts + (int64_t)b * (n_edges - 1), sums + (int64_t)b * (n_edges - 1), st)))
+      return rc;
+  }
+  return NB_OK;
+}

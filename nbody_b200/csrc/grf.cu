@@ -156,3 +156,87 @@ extern "C" int nb_grf_synthesize(nb_ctx* ctx, const double* pk_grid, const doubl
   }
   return NB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Second-order (2LPT) displacement of the lattice ICs (`realization_options['LPT'] = 2`,
+// Different_Sizes/Giant.param:70-72; the reference compares both orders in 1LPTvs2LPT/1vs2tlptplotter.py):
+//   ∇²φ1 = δ,   ∇²φ2 = Σ_{a>b} [φ1,aa φ1,bb − (φ1,ab)²],   ψ2 = ∇φ2
+// float64 throughout: one D2Z of δ, six Z2D of the second derivatives, one element-wise source kernel, one
+// D2Z of the source and three Z2D of the gradient.  Spectral factors per mode: k_a k_b / k² for φ1,ab of δ_k
+// (mixed derivatives use the Nyquist-zeroed gradient k like the first-order ψ: the real part of the complex
+// inverse transform the numpy form takes annihilates them there) and −i k_a / k² for ψ2 of the source.
+__global__ void __launch_bounds__(256)
+lpt2_spectral_kernel(const double2* __restrict__ in, int N, const double* __restrict__ kv, int a, int b, int grad,
+                     double inv_n3, double2* __restrict__ out) {
+  const int nzh = N / 2 + 1, nyq = (N % 2 == 0) ? N / 2 : -1;
+  const int64_t n = (int64_t)N * N * nzh, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += stride) {
+    const int iz = (int)(t % nzh), iy = (int)((t / nzh) % N), ix = (int)(t / ((int64_t)nzh * N));
+    const int idx[3] = {ix, iy, iz};
+    const double k[3] = {kv[ix], kv[iy], kv[iz]};
+    const double k2 = (k[0] * k[0] + k[1] * k[1]) + k[2] * k[2];
+    const double2 v = in[t];
+    double2 r = make_double2(0.0, 0.0);
+    if (k2 > 0.0) {
+      if (grad) {                       // psi2_a = IFFT(i k_a phi2_k), phi2_k = -src_k / k²
+        const double ka = idx[a] == nyq ? 0.0 : k[a];
+        const double f = -ka / k2 * inv_n3;
+        r = make_double2(-f * v.y, f * v.x);
+      } else {                          // phi1,ab = IFFT(-k_a k_b phi1_k), phi1_k = -delta_k / k²
+        double f;
+        if (a == b) f = k[a] * k[a];
+        else f = (idx[a] == nyq ? 0.0 : k[a]) * (idx[b] == nyq ? 0.0 : k[b]);
+        f = f / k2 * inv_n3;
+        r = make_double2(f * v.x, f * v.y);
+      }
+    }
+    out[t] = r;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+lpt2_source_kernel(const double* __restrict__ d, int64_t n3, double* __restrict__ src) {
+  // d: six fields xx, yy, zz, xy, xz, yz
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride) {
+    const double xx = d[t], yy = d[n3 + t], zz = d[2 * n3 + t], xy = d[3 * n3 + t], xz = d[4 * n3 + t],
+                 yz = d[5 * n3 + t];
+    src[t] = xx * yy + xx * zz + yy * zz - xy * xy - xz * xz - yz * yz;
+  }
+}
+
+// delta: (N,N,N) float64 (not modified); work: 6 N³ float64 of caller scratch; psi2_out: (3,N,N,N) float64
+extern "C" int nb_lpt2_displacement(nb_ctx* ctx, const double* delta, int N, const double* k_vals, double* work6,
+                                    double* psi2_out, void* stream) {
+  NB_REQUIRE(ctx && delta && k_vals && work6 && psi2_out, "NULL argument");
+  NB_REQUIRE(N >= 2, "bad N");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  const int64_t n3 = (int64_t)N * N * N, nspec = (int64_t)N * N * (N / 2 + 1);
+  void *dk = nullptr, *tmp = nullptr;
+  int rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_SPEC0, nspec * 16, &dk))) return rc;
+  if ((rc = nb_scratch(ctx, NB_SCR_SPEC1, nspec * 16, &tmp))) return rc;
+  cufftHandle fwd, inv;
+  if ((rc = nb_plan3d(ctx, N, CUFFT_D2Z, st, &fwd))) return rc;
+  if ((rc = nb_plan3d(ctx, N, CUFFT_Z2D, st, &inv))) return rc;
+  const double inv_n3 = 1.0 / (double)n3;
+  const int nblk = nb_grid_for(ctx, nspec, 256, 8);
+  NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)const_cast<double*>(delta), (cufftDoubleComplex*)dk));
+  const int pa[6] = {0, 1, 2, 0, 0, 1}, pb[6] = {0, 1, 2, 1, 2, 2};
+  for (int c = 0; c < 6; ++c) {
+    lpt2_spectral_kernel<<<nblk, 256, 0, st>>>((const double2*)dk, N, k_vals, pa[c], pb[c], 0, inv_n3, (double2*)tmp);
+    NB_LAUNCHED(ctx);
+    if ((rc = nb_exec_c2r(ctx, inv, NB_F64, tmp, work6 + c * n3, n3 * sizeof(double), st))) return rc;
+  }
+  // the source overwrites the first work field (each cell reads its six inputs before it writes)
+  lpt2_source_kernel<<<nb_grid_for(ctx, n3, 256, 8), 256, 0, st>>>(work6, n3, work6);
+  NB_LAUNCHED(ctx);
+  NB_CHECK_CUFFT(cufftExecD2Z(fwd, (cufftDoubleReal*)work6, (cufftDoubleComplex*)dk));
+  for (int c = 0; c < 3; ++c) {
+    lpt2_spectral_kernel<<<nblk, 256, 0, st>>>((const double2*)dk, N, k_vals, c, c, 1, inv_n3, (double2*)tmp);
+    NB_LAUNCHED(ctx);
+    if ((rc = nb_exec_c2r(ctx, inv, NB_F64, tmp, psi2_out + c * n3, n3 * sizeof(double), st))) return rc;
+  }
+  return NB_OK;
+}

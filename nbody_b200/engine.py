@@ -190,6 +190,44 @@ class Engine:
                                                     _prec_of(grids), self.stream), "nb_snapshot_delta_batch")
         return grids
 
+    def snapshot_pk_batch(self, pos_cat: torch.Tensor, offsets, boxsizes, N: int, n_edges: int = 300,
+                          window_power: int = 0, clip_mode: int = 0, clip_val: float = 0.0, closed_last: bool = True,
+                          kq_form: str = "inv_d", norms=None):
+        """B snapshots sharing the mesh size N -> (edges list, counts (B, n_edges-1) int64, sums float64) in one
+        library call (nb_snapshot_pk_batch; Plotter.py:205-238).  norms: per-snapshot factor on |δ_k|²
+        (default V / N⁶)."""
+        offsets = np.asarray(offsets, dtype=np.int64)
+        B = offsets.size - 1
+        boxsizes = np.asarray(boxsizes, dtype=np.float64).reshape(B)
+        if B < 1 or offsets[0] != 0 or np.any(np.diff(offsets) <= 0) or offsets[-1] != pos_cat.shape[0]:
+            raise ValueError("offsets must start at 0, increase and end at the particle count")
+        if pos_cat.dtype != torch.float64 or not pos_cat.is_contiguous():
+            raise ValueError("pos_cat must be a contiguous float64 (total,3) tensor")
+        N = int(N)
+        fn = {"inv_d": tables.sinc_table, "piN_L": tables.sinc_table_kq}[kq_form]
+        edges, thr, t0, t1, thi, k2t, st = [], [], [], [], [], [], []
+        for L in boxsizes:
+            e = tables.pk_edges(N, float(L), n_edges)
+            th, th_hi = tables.sqrt_thresholds(e)
+            edges.append(e); thr.append(th); t0.append(th[0]); t1.append(th[-1]); thi.append(th_hi)
+            k2t.append(tables.k_vals(N, float(L)) ** 2); st.append(fn(N, float(L)))
+        dev = self.device
+        up = lambda a, dt=np.float64: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(dev)   # noqa: E731
+        d_off, d_cell, d_np = up(offsets, np.int64), up(boxsizes / N), up(np.diff(offsets).astype(np.float64))
+        d_k2, d_s, d_thr = up(np.stack(k2t)), up(np.stack(st)), up(np.stack(thr))
+        h = lambda a: np.ascontiguousarray(a, dtype=np.float64)                                      # noqa: E731
+        h0, h1, hhi = h(t0), h(t1), h(thi)
+        hn = h(boxsizes ** 3 / float(N) ** 6 if norms is None else norms)
+        counts = torch.empty((B, n_edges - 1), dtype=torch.int64, device=dev)
+        sums = torch.empty((B, n_edges - 1), dtype=torch.float64, device=dev)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)                                                  # noqa: E731
+        _lib.check(self.lib.nb_snapshot_pk_batch(self.ctx, _ptr(pos_cat), _ptr(d_off), int(offsets[-1]), int(B),
+                                                 _ptr(d_cell), _ptr(d_np), N, _ptr(d_k2), _ptr(d_s), _ptr(d_thr),
+                                                 vp(h0), vp(h1), vp(hhi), int(n_edges), int(window_power),
+                                                 int(clip_mode), float(clip_val), vp(hn), int(bool(closed_last)),
+                                                 _ptr(counts), _ptr(sums), self.stream), "nb_snapshot_pk_batch")
+        return edges, counts, sums
+
     def sinc_tab(self, N, L, kq_form="inv_d"):
         fn = {"inv_d": tables.sinc_table, "piN_L": tables.sinc_table_kq}[kq_form]
         return self.table(("sinc", kq_form, N, float(L)), lambda: fn(N, L))
@@ -269,6 +307,18 @@ class Engine:
                                               int(bool(guard)), F64 if dtype == torch.float64 else F32,
                                               _ptr(delta), _ptr(psi), self.stream), "nb_grf_synthesize")
         return delta, psi
+
+    def lpt2_displacement(self, delta: torch.Tensor, L: float) -> torch.Tensor:
+        """(3,N,N,N) float64 second-order displacement field of the linear delta (nb_lpt2_displacement)."""
+        N = delta.shape[0]
+        if delta.dtype != torch.float64 or delta.shape != (N, N, N) or not delta.is_contiguous():
+            raise ValueError("delta must be a contiguous (N,N,N) float64 tensor")
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        work = torch.empty((6, N, N, N), dtype=torch.float64, device=self.device)
+        out = torch.empty((3, N, N, N), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.nb_lpt2_displacement(self.ctx, _ptr(delta), int(N), _ptr(kv), _ptr(work), _ptr(out),
+                                                 self.stream), "nb_lpt2_displacement")
+        return out
 
     # -- K3 ---------------------------------------------------------------------------
     def cic_gather(self, field: torch.Tensor, pos: torch.Tensor, cell: float, N: int, shift: float = 0.0,

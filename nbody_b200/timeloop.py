@@ -227,27 +227,16 @@ def second_order_growth(cosmo: Cosmology, a):
     return -3.0 / 7.0 * d1 * d1 * om_a ** (-1.0 / 143.0), 2.0 * om_a ** (6.0 / 11.0)
 
 
-def second_order_displacement(delta, L):
-    """ψ⁽²⁾ = ∇φ⁽²⁾ on the lattice from the linear δ(q) at D₊ = 1 (device tensor (n,n,n)):
+def second_order_displacement(delta, L, engine=None):
+    """ψ⁽²⁾ = ∇φ⁽²⁾ on the lattice from the linear δ(q) at D₊ = 1 (device tensor (n,n,n) float64):
     ∇²φ⁽¹⁾ = δ, ∇²φ⁽²⁾ = Σ_{i>j} [φ⁽¹⁾,ii φ⁽¹⁾,jj − (φ⁽¹⁾,ij)²], so that x = q + D₊ψ⁽¹⁾ + D₂ψ⁽²⁾
-    with ψ⁽¹⁾ = −∇φ⁽¹⁾ the K7 displacement.  Eight small FFTs of an IC-time field: cuFFT through
-    torch.fft, not a hot-path kernel."""
-    import torch
-    n = delta.shape[0]
-    kv = torch.as_tensor(tables.k_vals(n, L), dtype=torch.float64, device=delta.device)
-    kx, ky, kz = kv[:, None, None], kv[None, :, None], kv[None, None, :]
-    k2 = kx * kx + ky * ky + kz * kz
-    k2[0, 0, 0] = 1.0
-    phi_k = -torch.fft.fftn(delta.to(torch.float64)) / k2
-    phi_k[0, 0, 0] = 0.0
-
-    def dd(ka, kb):
-        return torch.fft.ifftn(-(ka * kb) * phi_k).real
-    pxx, pyy, pzz = dd(kx, kx), dd(ky, ky), dd(kz, kz)
-    src = pxx * pyy + pxx * pzz + pyy * pzz - dd(kx, ky) ** 2 - dd(kx, kz) ** 2 - dd(ky, kz) ** 2
-    phi2_k = -torch.fft.fftn(src) / k2
-    phi2_k[0, 0, 0] = 0.0
-    psi2 = torch.stack([torch.fft.ifftn(1j * ka * phi2_k).real for ka in (kx, ky, kz)])
+    with ψ⁽¹⁾ = −∇φ⁽¹⁾ the K7 displacement.  Runs behind the C-ABI (nb_lpt2_displacement: cuFFT for
+    the eleven transforms, two small kernels for the spectral factors and the source term); returns
+    (n³,3) in lattice order."""
+    from .engine import default_engine
+    eng = engine or default_engine()
+    d = delta if delta.is_cuda else delta.to(eng.device)
+    psi2 = eng.lpt2_displacement(d.to(dtype=d.dtype).contiguous(), float(L))
     return psi2.reshape(3, -1).t().contiguous()
 
 
@@ -287,7 +276,7 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
     mom = psi * (vel * cosmo.growth_rate(a_begin) * d_rel)
     if lpt == 2:
         d2, f2 = second_order_growth(cosmo, a_begin)
-        psi2 = second_order_displacement(delta, float(L))
+        psi2 = second_order_displacement(delta, float(L), engine=eng)
         disp = disp + psi2 * d2
         mom = mom + psi2 * (vel * f2 * d2)
     eng.displace_wrap(pos, disp.contiguous(), float(L))

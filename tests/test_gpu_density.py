@@ -276,3 +276,36 @@ def test_pk_binning_split_tail_units(api, monkeypatch, grid, N):
         kr, pr, cr = restate.compute_power_spectrum(delta, fromcic, L, N, return_counts=True)
         assert np.array_equal(c, cr) and np.array_equal(k, kr)
         assert np.abs(p / pr - 1).max() <= TOL
+
+
+def test_batched_snapshot_pk_matches_the_single_calls_and_the_reference(api, snap_test1, tmp_path):
+    """nb_snapshot_pk_batch (Different_Sizes/Plotter.py:205-238 without the process pool): ragged particle
+    sets, two box sizes, all three estimator variants; equal to the per-snapshot calls (same kernels) and to the
+    reference's own output for the 3giant32pm snapshot.  The run-directory walker reproduces the reference's
+    (method, N_in, ngrid, boxsize) bookkeeping on a directory of written snapshots."""
+    from nbody_b200 import snapshot
+    pos1, L1, _ = snap_test1
+    gp = golden("snap_giant32pm.npz")
+    g = golden("ref_pk_snapshot.npz")
+    sets = [gp["pos"], pos1[:30011], pos1, gp["pos"][5:]]
+    boxes = [1000.0, L1, L1, 1000.0]
+    for variant in ("plotter", "lpt", "power_compare"):
+        got = api.power_spectra_from_positions(sets, boxes, 32, variant=variant)
+        assert len(got) == 4
+        for (k, p), pos, L in zip(got, sets, boxes):
+            ks, ps = api.power_spectrum_from_positions(pos, L, 32, variant=variant)
+            assert np.array_equal(k, ks) and np.abs(p / ps - 1).max() <= 1e-6
+        if variant != "power_compare":
+            assert np.array_equal(got[0][0], g[f"{variant}_giant_k"])
+            assert np.abs(got[0][1] / g[f"{variant}_giant_p"] - 1).max() <= (2e-3 if variant == "plotter" else TOL)
+    assert api.power_spectra_from_positions([], [], 32) == []
+    # directory walk: two runs with the reference's naming, one of each method
+    for name, pos in (("3giant32pm", gp["pos"]), ("3giant32p3m", gp["pos"][::-1].copy())):
+        d = tmp_path / name / "snapshots"
+        d.mkdir(parents=True)
+        snapshot.write_snapshot(str(d / "snapshot_a=1.00.hdf5"), pos, np.zeros_like(pos), boxsize=1000.0)
+    (tmp_path / "notes").mkdir()
+    data = api.power_spectra_of_runs(str(tmp_path))
+    assert [m for m, _r in data] == [("p3m", 32, 32, 1000.0), ("pm", 32, 32, 1000.0)]
+    for _m, (k, p) in data:
+        assert np.array_equal(k, g["plotter_giant_k"]) and np.abs(p / g["plotter_giant_p"] - 1).max() <= 2e-3

@@ -177,3 +177,35 @@ def test_periodic_pp_steps_use_the_ewald_force():
     p, m = timeloop.evolve(st, c, eng.to_device(pos0), eng.to_device(mom0), edges)
     assert _pdiff(p.cpu().numpy(), p_ref, L) <= 1e-7 * L
     assert np.abs(m.cpu().numpy() - m_ref).max() <= 1e-4 * np.abs(m_ref).max()
+
+
+def test_second_order_displacement_analytic_and_restatement():
+    """nb_lpt2_displacement: closed form for two crossed plane waves, zero for a single one (Zel'dovich is
+    exact in 1-D), and the numpy restatement (complex FFTs, real part) on a random field."""
+    import torch
+    from nbody_b200 import timeloop
+    L, n = 100.0, 16
+    x = np.arange(n) * (L / n)
+    k = 2 * np.pi / L * 2
+    A, B = 0.3, -0.7
+    X, Y, _Z = np.meshgrid(x, x, x, indexing="ij")
+    delta = A * np.cos(k * X) + B * np.cos(k * Y)
+    got = timeloop.second_order_displacement(torch.from_numpy(delta), L).cpu().numpy()
+    want = np.stack([A * B / (2 * k) * np.sin(k * X) * np.cos(k * Y), A * B / (2 * k) * np.cos(k * X) * np.sin(k * Y),
+                     np.zeros_like(X)], axis=-1).reshape(-1, 3)
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+    rs = np.random.RandomState(4)
+    delta = rs.normal(size=(n, n, n))
+    delta -= delta.mean()
+    got = timeloop.second_order_displacement(torch.from_numpy(delta), L).cpu().numpy()
+    ref = numpy_second_order(delta, L)
+    assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max()
+    delta = 0.4 * np.cos(2 * np.pi / L * 3 * X + 0.3)
+    psi2 = timeloop.second_order_displacement(torch.from_numpy(delta), L).cpu().numpy()
+    assert np.abs(psi2).max() < 1e-12
+    for odd in (9, 12):                                   # odd mesh and a mesh that is not a power of two
+        d = rs.normal(size=(odd, odd, odd))
+        d -= d.mean()
+        got = timeloop.second_order_displacement(torch.from_numpy(d), L).cpu().numpy()
+        ref = numpy_second_order(d, L)
+        assert np.abs(got - ref).max() <= 1e-11 * np.abs(ref).max()
