@@ -163,8 +163,9 @@ extern "C" int nb_grf_synthesize(nb_ctx* ctx, const double* pk_grid, const doubl
 //   ∇²φ1 = δ,   ∇²φ2 = Σ_{a>b} [φ1,aa φ1,bb − (φ1,ab)²],   ψ2 = ∇φ2
 // float64 throughout: one D2Z of δ, six Z2D of the second derivatives, one element-wise source kernel, one
 // D2Z of the source and three Z2D of the gradient.  Spectral factors per mode: k_a k_b / k² for φ1,ab of δ_k
-// (mixed derivatives use the Nyquist-zeroed gradient k like the first-order ψ: the real part of the complex
-// inverse transform the numpy form takes annihilates them there) and −i k_a / k² for ψ2 of the source.
+// (a mixed derivative with exactly ONE index on its Nyquist plane is odd under k -> -k there, so the real part
+// the numpy form takes of the complex inverse transform annihilates it — like the first-order gradient; with both
+// indices on Nyquist planes the factor k_N² is even and stays) and −i k_a / k² for ψ2 of the source.
 __global__ void __launch_bounds__(256)
 lpt2_spectral_kernel(const double2* __restrict__ in, int N, const double* __restrict__ kv, int a, int b, int grad,
                      double inv_n3, double2* __restrict__ out) {
@@ -185,7 +186,7 @@ lpt2_spectral_kernel(const double2* __restrict__ in, int N, const double* __rest
       } else {                          // phi1,ab = IFFT(-k_a k_b phi1_k), phi1_k = -delta_k / k²
         double f;
         if (a == b) f = k[a] * k[a];
-        else f = (idx[a] == nyq ? 0.0 : k[a]) * (idx[b] == nyq ? 0.0 : k[b]);
+        else f = ((idx[a] == nyq) != (idx[b] == nyq)) ? 0.0 : k[a] * k[b];   // one Nyquist index: odd under k -> -k
         f = f / k2 * inv_n3;
         r = make_double2(f * v.x, f * v.y);
       }
@@ -195,7 +196,7 @@ lpt2_spectral_kernel(const double2* __restrict__ in, int N, const double* __rest
 }
 
 __global__ void __launch_bounds__(256)
-lpt2_source_kernel(const double* __restrict__ d, int64_t n3, double* __restrict__ src) {
+lpt2_source_kernel(const double* d, int64_t n3, double* src) {   // src may alias the first field
   // d: six fields xx, yy, zz, xy, xz, yz
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n3; t += stride) {

@@ -398,14 +398,20 @@ __device__ __forceinline__ float4 p3m_lds128(unsigned saddr) {
   return v;
 }
 
-template <int QD>
+template <int QD, int CAPC>
 __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const float* __restrict__ ty,
-                                          const float* __restrict__ tz, unsigned txs, unsigned cap4,
+                                          const float* __restrict__ tz, unsigned txs, unsigned cap4_rt,
                                           unsigned short* __restrict__ qcol, unsigned qbase, int vbeg, int vend,
                                           int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
                                           const P3m3Packed& k, double& ax, double& ay, double& az) {
+  // CAPC > 0: the tile capacity is a compile-time constant, so the y / z planes are immediate offsets of
+  // the running x address (the runtime form cost an LDCU + MOV + 2 LEA per group)
+  const unsigned cap4 = CAPC > 0 ? 4u * (unsigned)CAPC : cap4_rt;
   unsigned qa = qbase;
-  const unsigned qfull = qbase + (QD - 8) * 64;   // a group pushes at most 8 entries per lane
+  unsigned qfull = qbase + (QD - 8) * 64;   // a group pushes at most 8 entries per lane
+  // opaque to the optimiser: ptxas otherwise re-derives this limit from %tid, the CTA's shared window and the
+  // tile size in EVERY group (S2R, SHF, LOP3, 2 IMAD, 2 IADD3, 2 MOV: 9 of the 92 instructions of the loop)
+  asm volatile("" : "+r"(qfull));
   unsigned sx = txs + 4u * (unsigned)(vbeg + 4 * strm);
   const unsigned send = txs + 4u * (unsigned)vend;
   int v0 = vbeg + 4 * strm;
@@ -466,7 +472,7 @@ __host__ __device__ inline size_t p3m6_cta_bytes(int cap, int qd) {
          P3M6_WARPS * sizeof(unsigned short) * (size_t)(qd + 4) * 32;
 }
 
-template <int QD, int CTAS, bool MASK>
+template <int QD, int CTAS, bool MASK, int CAPC = 0>
 __global__ void __launch_bounds__(P3M6_WARPS * 32, CTAS)
 p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
@@ -475,6 +481,7 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   extern __shared__ __align__(16) unsigned char p3m6_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int li = lane & 7, strm = lane >> 3;
+  if (CAPC > 0) cap = CAPC;        // compile-time tile capacity: the y / z planes become immediate offsets
   float* tx = reinterpret_cast<float*>(p3m6_smem);
   float* ty = tx + cap;
   float* tz = ty + cap;
@@ -614,7 +621,7 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
                   nyi, nzi, k, ax, ay, az);
       else
 #endif
-        p3m6_pass<QD>(tx, ty, tz, txs, cap4, qcol, qbase, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
+        p3m6_pass<QD, CAPC>(tx, ty, tz, txs, cap4, qcol, qbase, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
       ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
       az += __shfl_xor_sync(0xffffffffu, az, 8);
       ax += __shfl_xor_sync(0xffffffffu, ax, 16); ay += __shfl_xor_sync(0xffffffffu, ay, 16);
@@ -672,9 +679,9 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
     const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nrun;
     const int64_t nblk = nunits < cap ? nunits : cap;
-    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<QD6, 6, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem6));
-    p3m_short_v6_kernel<QD6, 6, false><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<QD6, 6, false, CAP6>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem6));
+    p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
         (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, CAP6,
         ovf_list, ovf_count);
     NB_LAUNCHED(ctx);

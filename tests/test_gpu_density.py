@@ -294,7 +294,7 @@ def test_batched_snapshot_pk_matches_the_single_calls_and_the_reference(api, sna
         assert len(got) == 4
         for (k, p), pos, L in zip(got, sets, boxes):
             ks, ps = api.power_spectrum_from_positions(pos, L, 32, variant=variant)
-            assert np.array_equal(k, ks) and np.abs(p / ps - 1).max() <= 1e-6
+            assert np.array_equal(k, ks) and np.abs(p / ps - 1).max() <= TOL   # two deposit kernels: float32 sums in another order
         if variant != "power_compare":
             assert np.array_equal(got[0][0], g[f"{variant}_giant_k"])
             assert np.abs(got[0][1] / g[f"{variant}_giant_p"] - 1).max() <= (2e-3 if variant == "plotter" else TOL)
