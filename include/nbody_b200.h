@@ -327,6 +327,25 @@ int nb_slab_pack(nb_ctx* ctx, const void* src, void* dst, int nxl, int G, int ny
 int nb_slab_unpack(nb_ctx* ctx, const void* src, void* dst, int nxl, int G, int nyl, int nzh, void* stream);
 int nb_slab_owner(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N, int planes_per_rank,
                   int32_t* owner, int64_t* counts, int G, void* stream);
+/* Device-side particle exchange of the slab decomposition (no reference counterpart; replaces eager mask /
+ * nonzero / cat code and its host round trips).
+ * nb_halo_select: positions with x < lo_edge -> out_lo, x >= hi_edge -> out_hi (each (cap,3) float64; unused rows
+ *   stay NaN, which nb_cell_sort skips, so neighbours can exchange the buffers at fixed size); counts2 (device
+ *   int32[2]) = true numbers (> cap means overflow: rows beyond cap were dropped).
+ * nb_migrate_split: particles with owner != rank (owner from nb_slab_owner) -> send_prev / send_next ((cap,6):
+ *   pos, mom), their row indices -> holes (2 cap); counts4 (device int32) = {to_prev, to_next, holes, far} where
+ *   far = particles that crossed more than one slab (not moved).
+ * nb_migrate_merge: na + nb arrivals fill the first holes / are appended behind row np; with more leavers than
+ *   arrivals the tail is compacted into the remaining holes.  work: 3 (n_holes - na - nb) + 2 int32 of device
+ *   scratch in that case.  *new_np_host = np + na + nb - n_holes. */
+int nb_halo_select(nb_ctx* ctx, const double* pos, int64_t np, double lo_edge, double hi_edge, double* out_lo,
+                   double* out_hi, int cap, int32_t* counts2, void* stream);
+int nb_migrate_split(nb_ctx* ctx, const double* pos, const double* mom, int64_t np, const int32_t* owner, int rank,
+                     int prev, int next, double* send_prev, double* send_next, int cap, int32_t* holes,
+                     int32_t* counts4, void* stream);
+int nb_migrate_merge(nb_ctx* ctx, double* pos, double* mom, int64_t np, const int32_t* holes, int n_holes,
+                     const double* recv_a, int na, const double* recv_b, int nb, int32_t* work,
+                     int64_t* new_np_host, void* stream);
 int nb_grid_add(nb_ctx* ctx, float* dst, const float* src, int64_t n, void* stream);
 
 /* ---- batched snapshot -> delta -------------------------------------------

@@ -70,6 +70,10 @@ PROTOTYPES = {
     "nb_slab_pack": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp]),
     "nb_slab_unpack": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp]),
     "nb_slab_owner": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "nb_halo_select": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_f64, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "nb_migrate_split": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp]),
+    "nb_migrate_merge": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp,
+                                 C.POINTER(c_i64), c_vp]),
     "nb_grid_add": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp]),
     "nb_snapshot_delta_batch": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i32, c_vp, c_i32, c_vp, c_vp, c_i32,
                                         c_vp]),

@@ -148,3 +148,179 @@ extern "C" int nb_grid_add(nb_ctx* ctx, float* dst, const float* src, int64_t n,
   NB_LAUNCHED(ctx);
   return NB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// Device-side particle exchange of the slab decomposition (the halo selection and
+// the migration were eager boolean masks / nonzero / cat with two host round trips per step).
+//
+// Halo: the positions within r_cut of the two slab faces are appended to two fixed-capacity send
+// buffers (warp-aggregated atomics); unused rows stay NaN (the caller memsets the buffers to 0xFF), and
+// nb_cell_sort skips NaN rows — so the neighbours exchange FIXED-size buffers and nothing about the
+// counts has to reach the host.  counts[0..1] still receive the true numbers (overflow check, folded
+// into the one host sync of the step).
+__device__ __forceinline__ int slab_warp_append(bool take, int* counter) {
+  const unsigned m = __ballot_sync(__activemask(), take);
+  if (!take) return -1;
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(counter, __popc(m));
+  base = __shfl_sync(m, base, leader);
+  return base + __popc(m & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(256)
+halo_select_kernel(const double* __restrict__ pos, int64_t np, double lo_edge, double hi_edge,
+                   double* __restrict__ out_lo, double* __restrict__ out_hi, int cap, int* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t nround = (np + stride - 1) / stride;
+  for (int64_t r = 0; r < nround; ++r) {                 // whole warps stay in the loop (ballots)
+    const int64_t p = r * stride + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = p < np;
+    double x = 0.0, y = 0.0, z = 0.0;
+    if (in) { x = pos[3 * p]; y = pos[3 * p + 1]; z = pos[3 * p + 2]; }
+    const int slo = slab_warp_append(in && x < lo_edge, counts);
+    if (slo >= 0 && slo < cap) { out_lo[3 * slo] = x; out_lo[3 * slo + 1] = y; out_lo[3 * slo + 2] = z; }
+    const int shi = slab_warp_append(in && x >= hi_edge, counts + 1);
+    if (shi >= 0 && shi < cap) { out_hi[3 * shi] = x; out_hi[3 * shi + 1] = y; out_hi[3 * shi + 2] = z; }
+  }
+}
+
+extern "C" int nb_halo_select(nb_ctx* ctx, const double* pos, int64_t np, double lo_edge, double hi_edge,
+                              double* out_lo, double* out_hi, int cap, int32_t* counts2, void* stream) {
+  NB_REQUIRE(ctx && out_lo && out_hi && counts2 && (np == 0 || pos) && cap >= 1, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  NB_CHECK_CUDA(cudaMemsetAsync(out_lo, 0xFF, sizeof(double) * 3 * (size_t)cap, st));   // all-ones = NaN
+  NB_CHECK_CUDA(cudaMemsetAsync(out_hi, 0xFF, sizeof(double) * 3 * (size_t)cap, st));
+  NB_CHECK_CUDA(cudaMemsetAsync(counts2, 0, 2 * sizeof(int32_t), st));
+  if (np == 0) return NB_OK;
+  halo_select_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(pos, np, lo_edge, hi_edge, out_lo, out_hi, cap,
+                                                                   counts2);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+// Migration, step 1: the particles whose owner (nb_slab_owner) is not `rank` are copied — position and
+// momentum, 6 doubles — to the send buffer of the previous (owner == prev) or next (owner == next) slab,
+// and their rows are recorded as holes.  counts4 = {to_prev, to_next, holes, far}: `far` counts particles
+// that crossed more than one slab (left in place; the caller falls back to its general exchange).
+__global__ void __launch_bounds__(256)
+migrate_split_kernel(const double* __restrict__ pos, const double* __restrict__ mom, int64_t np,
+                     const int* __restrict__ owner, int rank, int prev, int next, double* __restrict__ send_prev,
+                     double* __restrict__ send_next, int cap, int* __restrict__ holes, int* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t nround = (np + stride - 1) / stride;
+  for (int64_t r = 0; r < nround; ++r) {
+    const int64_t p = r * stride + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int o = p < np ? owner[p] : rank;
+    const bool leaves = o != rank;
+    const bool to_prev = leaves && o == prev;                  // world == 2: prev == next, everything goes "prev"
+    const bool to_next = leaves && !to_prev && o == next;
+    const bool far = leaves && !to_prev && !to_next;
+    const int sp = slab_warp_append(to_prev, counts);
+    const int sn = slab_warp_append(to_next, counts + 1);
+    const int sh = slab_warp_append(to_prev || to_next, counts + 2);
+    if (far) atomicAdd(counts + 3, 1);
+    double* dst = nullptr;
+    if (sp >= 0 && sp < cap) dst = send_prev + 6 * (int64_t)sp;
+    if (sn >= 0 && sn < cap) dst = send_next + 6 * (int64_t)sn;
+    if (dst) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { dst[c] = pos[3 * p + c]; dst[3 + c] = mom[3 * p + c]; }
+    }
+    if (sh >= 0 && sh < 2 * cap) holes[sh] = (int)p;
+  }
+}
+
+extern "C" int nb_migrate_split(nb_ctx* ctx, const double* pos, const double* mom, int64_t np,
+                                const int32_t* owner, int rank, int prev, int next, double* send_prev,
+                                double* send_next, int cap, int32_t* holes, int32_t* counts4, void* stream) {
+  NB_REQUIRE(ctx && owner && send_prev && send_next && holes && counts4 && (np == 0 || (pos && mom)) && cap >= 1,
+             "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  NB_CHECK_CUDA(cudaMemsetAsync(counts4, 0, 4 * sizeof(int32_t), st));
+  if (np == 0) return NB_OK;
+  migrate_split_kernel<<<nb_grid_for(ctx, np, 256, 16), 256, 0, st>>>(pos, mom, np, owner, rank, prev, next,
+                                                                     send_prev, send_next, cap, holes, counts4);
+  NB_LAUNCHED(ctx);
+  return NB_OK;
+}
+
+// Migration, step 2 (all counts known on the host after the step's one synchronisation): the n_in arrivals
+// (rows of recv_a then recv_b, 6 doubles each) fill the first holes, a surplus is appended behind row np;
+// if more particles left than arrived, the remaining holes below the new end are filled with the non-hole
+// rows of the tail.  pos / mom must have room for np + max(0, n_in - n_holes) rows.
+__global__ void __launch_bounds__(256)
+migrate_fill_kernel(double* __restrict__ pos, double* __restrict__ mom, int64_t np, const int* __restrict__ holes,
+                    int n_holes, const double* __restrict__ recv_a, int na, const double* __restrict__ recv_b, int nb) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= na + nb) return;
+  const double* src = k < na ? recv_a + 6 * (int64_t)k : recv_b + 6 * (int64_t)(k - na);
+  const int64_t d = k < n_holes ? (int64_t)holes[k] : np + (k - n_holes);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { pos[3 * d + c] = src[c]; mom[3 * d + c] = src[3 + c]; }
+}
+
+__global__ void __launch_bounds__(256)
+migrate_tailmark_kernel(const int* __restrict__ holes, int first, int n_rem, int64_t new_n, int* __restrict__ tail_is_hole) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_rem) return;
+  const int h = holes[first + t];
+  if (h >= new_n) tail_is_hole[h - new_n] = 1;
+}
+
+__global__ void __launch_bounds__(256)
+migrate_pair_kernel(const int* __restrict__ holes, int first, int n_rem, int64_t new_n,
+                    const int* __restrict__ tail_is_hole, int* __restrict__ src, int* __restrict__ dst,
+                    int* __restrict__ cnt2) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_rem) return;
+  if (!tail_is_hole[t]) src[atomicAdd(cnt2, 1)] = (int)(new_n + t);       // a live particle in the tail
+  const int h = holes[first + t];
+  if (h < new_n) dst[atomicAdd(cnt2 + 1, 1)] = h;                          // an open slot below the new end
+}
+
+__global__ void __launch_bounds__(256)
+migrate_move_kernel(double* __restrict__ pos, double* __restrict__ mom, const int* __restrict__ src,
+                    const int* __restrict__ dst, const int* __restrict__ cnt2, int n_rem) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_rem || k >= cnt2[0]) return;
+  const int64_t s = src[k], d = dst[k];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { pos[3 * d + c] = pos[3 * s + c]; mom[3 * d + c] = mom[3 * s + c]; }
+}
+
+// work: 3 * n_rem + 2 int32 of scratch (n_rem = max(0, n_holes - n_in)); returns the new row count in *new_np_host
+extern "C" int nb_migrate_merge(nb_ctx* ctx, double* pos, double* mom, int64_t np, const int32_t* holes,
+                                int n_holes, const double* recv_a, int na, const double* recv_b, int nb,
+                                int32_t* work, int64_t* new_np_host, void* stream) {
+  NB_REQUIRE(ctx && new_np_host && n_holes >= 0 && na >= 0 && nb >= 0, "bad arguments");
+  NB_REQUIRE((n_holes == 0 || holes) && (na == 0 || recv_a) && (nb == 0 || recv_b), "NULL buffer");
+  NB_REQUIRE((na + nb == 0 && n_holes == 0) || (pos && mom), "NULL particle arrays");
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  const int n_in = na + nb;
+  if (n_in > 0) {
+    migrate_fill_kernel<<<(n_in + 255) / 256, 256, 0, st>>>(pos, mom, np, holes, n_holes, recv_a, na, recv_b, nb);
+    NB_LAUNCHED(ctx);
+  }
+  const int n_rem = n_holes - n_in;
+  *new_np_host = np + n_in - n_holes;
+  if (n_rem > 0) {
+    NB_REQUIRE(work, "work buffer needed when more particles leave than arrive");
+    const int64_t new_n = np - n_rem;
+    int* tail = work;
+    int* src = work + n_rem;
+    int* dst = src + n_rem;
+    int* cnt2 = dst + n_rem;
+    NB_CHECK_CUDA(cudaMemsetAsync(tail, 0, sizeof(int) * (size_t)n_rem, st));
+    NB_CHECK_CUDA(cudaMemsetAsync(cnt2, 0, 2 * sizeof(int), st));
+    const int g = (n_rem + 255) / 256;
+    migrate_tailmark_kernel<<<g, 256, 0, st>>>(holes, n_in, n_rem, new_n, tail);
+    migrate_pair_kernel<<<g, 256, 0, st>>>(holes, n_in, n_rem, new_n, tail, src, dst, cnt2);
+    migrate_move_kernel<<<g, 256, 0, st>>>(pos, mom, src, dst, cnt2, n_rem);
+    ctx->launches += 3;
+  }
+  return NB_OK;
+}

@@ -7,7 +7,8 @@
 //                       coordinates (computed in float64, then rounded), so pair separations
 //                       keep ~1e-7·cs absolute accuracy independent of the box size;
 //   perm[slot]        = original particle index;
-//   cell_start[c]     = first slot of cell c = (cx*ncs + cy)*ncs + cz ; cell_start[ncs³] = Np.
+//   cell_start[c]     = first slot of cell c = (cx*ncs + cy)*ncs + cz ; cell_start[ncs³] = number of
+//                       valid particles (rows whose x is NaN are skipped: unused halo-buffer slots).
 #include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
@@ -28,6 +29,10 @@ sort_count_kernel(const double* __restrict__ pos, int64_t np, double L, double c
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
     double r;
+    if (!(pos[3 * p] == pos[3 * p])) {      // NaN row: an unused slot of a fixed-capacity halo buffer (nb_halo_select)
+      cell_of[p] = -1;
+      continue;
+    }
     const int cx = sort_cell_coord(pos[3 * p], L, inv_cs, ncs, &r, cs);
     const int cy = sort_cell_coord(pos[3 * p + 1], L, inv_cs, ncs, &r, cs);
     const int cz = sort_cell_coord(pos[3 * p + 2], L, inv_cs, ncs, &r, cs);
@@ -44,6 +49,7 @@ sort_scatter_kernel(const double* __restrict__ pos, int64_t np, double L, double
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
     const int c = cell_of[p];
+    if (c < 0) continue;
     const int slot = cell_start[c] + atomicAdd(&fill[c], 1);
     double rx, ry, rz;
     sort_cell_coord(pos[3 * p], L, inv_cs, ncs, &rx, cs);

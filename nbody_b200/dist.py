@@ -103,6 +103,24 @@ class TorchComm:
             w.wait()
         return recv
 
+    def shift_var(self, send: torch.Tensor, n_send: int, recv: torch.Tensor, n_recv: int, delta: int):
+        """First n_send rows of `send` -> rank+delta, n_recv rows <- rank-delta into `recv` (both sides know
+        the sizes; zero-size messages are skipped on both ends)."""
+        if self.world == 1:
+            if n_recv:
+                recv[:n_recv].copy_(send[:n_send])
+            return recv
+        dst, src = (self.rank + delta) % self.world, (self.rank - delta) % self.world
+        ops = []
+        if n_send:
+            ops.append(self.dist.P2POp(self.dist.isend, send[:n_send], dst, self.group))
+        if n_recv:
+            ops.append(self.dist.P2POp(self.dist.irecv, recv[:n_recv], src, self.group))
+        if ops:
+            for w in self.dist.batch_isend_irecv(ops):
+                w.wait()
+        return recv
+
     def all_gather(self, out: torch.Tensor, inp: torch.Tensor):
         if self.world == 1:
             out.view(-1).copy_(inp.view(-1))
@@ -187,6 +205,13 @@ class ThreadComm:
     def shift(self, send, recv, delta):
         got = self._swap(send)
         recv.copy_(got[(self.rank - delta) % self.world])
+        self._done()
+        return recv
+
+    def shift_var(self, send, n_send, recv, n_recv, delta):
+        got = self._swap(send[:n_send])
+        if n_recv:
+            recv[:n_recv].copy_(got[(self.rank - delta) % self.world])
         self._done()
         return recv
 
@@ -366,6 +391,11 @@ class DistForceStepper:
             raise ValueError(f"unknown force method {cfg.method!r}")
         self._acc = None
         self._pbuf = self._mbuf = None          # capacity buffers: rows [0,n) own particles, then halo / arrivals
+        self._hbuf = self._hcounts = self._hover = None
+        self._mig = None
+        # device-side halo selection / migration (nb_halo_select, nb_migrate_*): one host sync per step;
+        # False keeps the eager torch exchange (reference implementation of the same bookkeeping, tests)
+        self.device_exchange = True
         self.mesh = None
         self._mark = lambda name, fn: fn()      # bench.py installs a CUDA-event recorder per step
         if cfg.method in ("pm", "p3m"):
@@ -384,17 +414,38 @@ class DistForceStepper:
             self._acc = torch.empty((max(n, 1), 3), dtype=torch.float64, device=self.eng.device)
         return self._acc[:n]
 
+    def _halo_cap(self, n):
+        """Rows of one halo buffer: twice the uniform-density expectation n r_cut / slab width."""
+        c, lay = self.cfg, self.mesh.lay
+        return max(4096, int(2.0 * n * c.r_cut / (lay.nxl * c.cell)) + 1024)
+
+    def _mig_cap(self, n):
+        return max(4096, n // 8)
+
+    def _extra_rows(self, n):
+        """Rows behind the own particles: both received halo buffers (P3M) or the arrivals of a migration."""
+        if self.world == 1 or self.mesh is None:
+            return 0
+        return max(2 * self._halo_cap(n) if self.cfg.method == "p3m" else 0, 2 * self._mig_cap(n))
+
     def _own(self, pos, mom=None):
         """pos / mom as views (rows [0,n)) of this stepper's capacity buffers.  Halo copies and
         migrating particles are appended behind row n in place, so a step allocates nothing of
         the particle set's size (a growing torch.cat per step cost cudaMalloc stalls of 10+ ms
         on 4 GPUs).  Tensors that are already such views are returned as they are."""
         n = pos.shape[0]
-        if self._pbuf is None or self._pbuf.shape[0] < n + max(n // 8, 4096):
-            cap = n + max(n // 5, 65536)
+        need = n + self._extra_rows(n)
+        if self._pbuf is None or self._pbuf.shape[0] < need:
+            cap = need + max(n // 10, 16384)
             old_p, old_m = self._pbuf, self._mbuf
             self._pbuf = torch.empty((cap, 3), dtype=torch.float64, device=self.eng.device)
             self._mbuf = torch.empty((cap, 3), dtype=torch.float64, device=self.eng.device)
+            if old_p is not None and pos.data_ptr() == old_p.data_ptr():      # grown in flight: keep the contents
+                self._pbuf[:n].copy_(old_p[:n])
+                pos = self._pbuf[:n]
+                if mom is not None and mom.data_ptr() == old_m.data_ptr():
+                    self._mbuf[:n].copy_(old_m[:n])
+                    mom = self._mbuf[:n]
             del old_p, old_m
         if pos.data_ptr() != self._pbuf.data_ptr():
             self._pbuf[:n].copy_(pos)
@@ -446,15 +497,40 @@ class DistForceStepper:
         got = self.comm.exchange_var(send)
         return torch.cat([g for g in got if g.shape[0]]) if any(g.shape[0] for g in got) else pos.new_empty((0, 3))
 
+    def _halo_device(self, pos):
+        """Halo exchange without the host: nb_halo_select fills two fixed-capacity buffers (NaN beyond the
+        selected rows), the neighbours swap them, and the received buffers land right behind the own rows of
+        the capacity buffer — nb_cell_sort skips the NaN rows.  Returns the (n + 2 cap, 3) view."""
+        c, lay, eng = self.cfg, self.mesh.lay, self.eng
+        n = pos.shape[0]
+        pos, _ = self._own(pos)
+        cap = self._halo_cap(n)
+        if self._hbuf is None or self._hbuf.shape[1] != cap:
+            self._hbuf = torch.empty((2, cap, 3), dtype=torch.float64, device=eng.device)
+            self._hcounts = torch.zeros(2, dtype=torch.int32, device=eng.device)
+        x_lo, x_hi = lay.x0 * c.cell, (lay.x0 + lay.nxl) * c.cell
+        eng.halo_select(pos, x_lo + c.r_cut, x_hi - c.r_cut, self._hbuf[0], self._hbuf[1], self._hcounts)
+        over = (self._hcounts > cap).any().to(torch.int64)        # checked at the step's one host sync
+        self._hover = over if self._hover is None else torch.maximum(self._hover, over)
+        dst = self._pbuf[n:n + 2 * cap]
+        self.comm.shift(self._hbuf[0], dst[:cap], -1)       # my low face -> previous slab; I receive the next slab's
+        self.comm.shift(self._hbuf[1], dst[cap:], +1)       # my high face -> next slab; I receive the previous slab's
+        return self._pbuf[:n + 2 * cap]
+
     def short_range(self, pos, acc, accumulate=True):
         c, mk = self.cfg, self._mark
-        halo = mk("halo_exchange", lambda: self.halo_exchange(pos))
-        n, h = pos.shape[0], int(halo.shape[0])
-        if h and self._pbuf is not None and pos.data_ptr() == self._pbuf.data_ptr() and n + h <= self._pbuf.shape[0]:
-            self._pbuf[n:n + h].copy_(halo)          # halo copies sit right behind the own particles
-            allp = self._pbuf[:n + h]
+        n = pos.shape[0]
+        if self.world > 1 and self.device_exchange:
+            allp = mk("halo_exchange", lambda: self._halo_device(pos))
+            h = allp.shape[0] - n
         else:
-            allp = torch.cat([pos, halo]) if h else pos
+            halo = mk("halo_exchange", lambda: self.halo_exchange(pos))
+            h = int(halo.shape[0])
+            if h and self._pbuf is not None and pos.data_ptr() == self._pbuf.data_ptr() and n + h <= self._pbuf.shape[0]:
+                self._pbuf[n:n + h].copy_(halo)          # halo copies sit right behind the own particles
+                allp = self._pbuf[:n + h]
+            else:
+                allp = torch.cat([pos, halo]) if h else pos
         self.last_halo = h
         sorted4, perm, cell_start = mk("cell_sort", lambda: self.eng.cell_sort(allp, c.boxsize, self.ncs, mass=1.0))
         # only the sort cells that overlap this rank's x-slab can hold own (i-) particles: cells are
@@ -498,14 +574,65 @@ class DistForceStepper:
         return acc
 
     # -- migration ----------------------------------------------------------------------------------
+    def _flags(self, far=None):
+        """(far movers, particles outside the slab at the deposit, halo-buffer overflow) as a device int64[3]."""
+        z = torch.zeros(1, dtype=torch.int64, device=self.eng.device)
+        hov = self._hover.reshape(1) if self._hover is not None else z
+        self._hover = None
+        return torch.cat([z if far is None else far.reshape(1).to(torch.int64), self.mesh.n_outside.sum().reshape(1), hov])
+
+    def _raise_flags(self, n_out_slab, h_over):
+        from ._lib import NbodyError
+        if n_out_slab:
+            raise NbodyError(f"{n_out_slab} particle(s) were outside their rank's x-slab at the deposit of this step "
+                             "(shard with dist.shard_particles / keep the set returned by step())")
+        if h_over:
+            raise NbodyError("halo buffer overflow: more particles within r_cut of a slab face than twice the "
+                             "uniform-density expectation (raise DistForceStepper._halo_cap)")
+
     def migrate(self, pos, mom):
         """Hand particles that drifted out of this rank's x-slab to their new owner.  Only the
         leavers and the arrivals are moved: arrivals fill the leavers' slots, a surplus is
-        appended, a deficit is closed by moving particles from the tail into the open slots."""
+        appended, a deficit is closed by moving particles from the tail into the open slots.
+        Device path (default): nb_slab_owner + nb_migrate_split pick and pack the leavers, the counts go to the
+        neighbours as two 4-byte messages, ONE host synchronisation reads them together with the step's error
+        flags, then exact-size neighbour messages and nb_migrate_merge.  Particles that crossed more than one
+        slab in a step send every rank through the general (eager) exchange below."""
         c, lay = self.cfg, self.mesh.lay
         if self.world == 1:
             return pos, mom
         n = pos.shape[0]
+        if self.device_exchange:
+            eng, dev = self.eng, self.eng.device
+            pos, mom = self._own(pos, mom)
+            cap = self._mig_cap(n)
+            if self._mig is None or self._mig["cap"] != cap:
+                self._mig = {"cap": cap, "send": torch.empty((2, cap, 6), dtype=torch.float64, device=dev),
+                             "recv": torch.empty((2, cap, 6), dtype=torch.float64, device=dev),
+                             "holes": torch.empty(2 * cap, dtype=torch.int32, device=dev),
+                             "counts": torch.zeros(4, dtype=torch.int32, device=dev),
+                             "rc": torch.zeros(2, dtype=torch.int32, device=dev)}
+            mg = self._mig
+            prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
+            owner, _ = eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world, want_counts=False)
+            eng.migrate_split(pos, mom, owner, self.rank, prev, nxt, mg["send"][0], mg["send"][1], mg["holes"],
+                              mg["counts"])
+            # my "to previous" count -> previous rank, I receive the next rank's (its particles coming down to me)
+            self.comm.shift(mg["counts"][0:1], mg["rc"][0:1], -1)
+            self.comm.shift(mg["counts"][1:2], mg["rc"][1:2], +1)
+            # general path wanted by anyone: a particle crossed more than one slab, or a buffer is too small
+            general = mg["counts"][3].to(torch.int64) + (mg["counts"][:2] > cap).any() + (mg["rc"] > cap).any()
+            flags = self._flags(far=general)
+            self.comm.all_reduce(flags, "max")
+            host = torch.cat([mg["counts"].to(torch.int64), mg["rc"].to(torch.int64), flags]).tolist()   # THE host sync
+            n_prev, n_next, n_holes, _far, r_next, r_prev, general_any, n_out_slab, h_over = (int(v) for v in host)
+            self._raise_flags(n_out_slab, h_over)
+            if general_any == 0:
+                self.comm.shift_var(mg["send"][0], n_prev, mg["recv"][0], r_next, -1)
+                self.comm.shift_var(mg["send"][1], n_next, mg["recv"][1], r_prev, +1)
+                new_n = eng.migrate_merge(self._pbuf, self._mbuf, n, mg["holes"], n_holes, mg["recv"][0], r_next,
+                                          mg["recv"][1], r_prev)
+                return self._pbuf[:new_n], self._mbuf[:new_n]
         owner, counts = self.eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world)
         # leavers of this step and the particles the deposit found outside the slab (wrong sharding on entry)
         moved = torch.stack([n - counts[self.rank], self.mesh.n_outside.sum()])
@@ -563,6 +690,9 @@ class DistForceStepper:
         self._gather(pos, None, acc, 0.0, 0.0)
         if c.method == "p3m":
             self.short_range(pos, acc, accumulate=True)
+            if self._hover is not None:
+                h_over, self._hover = int(self._hover.item()), None
+                self._raise_flags(0, h_over)
         return acc
 
     def step(self, pos, mom, dt_kick, dt_drift, mark=None, n_total: int = 0, periodic_pp=False):

@@ -578,14 +578,40 @@ class Engine:
         _lib.check(self.lib.nb_slab_unpack(self.ctx, _ptr(src), _ptr(dst), int(nxl), int(G), int(nyl), int(nzh),
                                            self.stream), "nb_slab_unpack")
 
-    def slab_owner(self, pos, cell, N, planes_per_rank, G):
+    def slab_owner(self, pos, cell, N, planes_per_rank, G, want_counts=True):
         self._check_pos(pos)
         owner = torch.empty(pos.shape[0], dtype=torch.int32, device=self.device)
-        counts = torch.empty(G, dtype=torch.int64, device=self.device)
+        counts = torch.empty(G, dtype=torch.int64, device=self.device) if want_counts else None
         _lib.check(self.lib.nb_slab_owner(self.ctx, _ptr(pos), pos.shape[0], float(cell), int(N),
                                           int(planes_per_rank), _ptr(owner), _ptr(counts), int(G), self.stream),
                    "nb_slab_owner")
         return owner, counts
+
+    def halo_select(self, pos, lo_edge: float, hi_edge: float, out_lo, out_hi, counts2):
+        """Rows with x < lo_edge -> out_lo, x >= hi_edge -> out_hi ((cap,3) float64, unused rows NaN);
+        counts2: device int32[2] (true counts, may exceed cap)."""
+        self._check_pos(pos)
+        cap = out_lo.shape[0]
+        _lib.check(self.lib.nb_halo_select(self.ctx, _ptr(pos), pos.shape[0], float(lo_edge), float(hi_edge),
+                                           _ptr(out_lo), _ptr(out_hi), int(cap), _ptr(counts2), self.stream),
+                   "nb_halo_select")
+
+    def migrate_split(self, pos, mom, owner, rank: int, prev: int, nxt: int, send_prev, send_next, holes, counts4):
+        self._check_pos(pos)
+        _lib.check(self.lib.nb_migrate_split(self.ctx, _ptr(pos), _ptr(mom), pos.shape[0], _ptr(owner), int(rank),
+                                             int(prev), int(nxt), _ptr(send_prev), _ptr(send_next),
+                                             int(send_prev.shape[0]), _ptr(holes), _ptr(counts4), self.stream),
+                   "nb_migrate_split")
+
+    def migrate_merge(self, pos_buf, mom_buf, n: int, holes, n_holes: int, recv_a, na: int, recv_b, nb: int) -> int:
+        """Arrivals into the holes / behind row n of the capacity buffers; returns the new row count."""
+        n_rem = max(0, int(n_holes) - int(na) - int(nb))
+        work = torch.empty(3 * n_rem + 2, dtype=torch.int32, device=self.device) if n_rem else None
+        out = C.c_int64(0)
+        _lib.check(self.lib.nb_migrate_merge(self.ctx, _ptr(pos_buf), _ptr(mom_buf), int(n), _ptr(holes), int(n_holes),
+                                             _ptr(recv_a), int(na), _ptr(recv_b), int(nb), _ptr(work), C.byref(out),
+                                             self.stream), "nb_migrate_merge")
+        return int(out.value)
 
     def grid_add(self, dst, src):
         if dst.dtype != torch.float32 or src.dtype != torch.float32 or dst.numel() != src.numel():

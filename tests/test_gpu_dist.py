@@ -78,17 +78,20 @@ def test_sharded_pp(world):
     assert err(a, oforce.accel(cfg, pos)) <= TOL
 
 
-@pytest.mark.parametrize("method", ["pm", "p3m"])
-def test_sharded_step_with_migration(method):
+@pytest.mark.parametrize("device_exchange", [True, False])
+@pytest.mark.parametrize("method,world", [("pm", 2), ("p3m", 2), ("pm", 4)])
+def test_sharded_step_with_migration(method, world, device_exchange):
     """A large drift moves particles across slab faces: after the step every rank holds exactly
-    the particles of its slab and the union equals the oracle's step."""
-    world, L, n, N = 2, 500.0, 12, 24
+    the particles of its slab and the union equals the oracle's step.  Both exchange implementations: the
+    device kernels (nb_halo_select / nb_migrate_*, one host sync per step) and the eager torch bookkeeping."""
+    L, n, N = 500.0, 12, 24
     pos = zeldovich_particles(n, L, seed=21)
     rs = np.random.RandomState(1)
     mom = rs.normal(scale=30.0, size=pos.shape)
     cfg = cfg_for(method, n, N, L, interlace=(True, True), G=1.0, mass=1.5, a=0.5)
 
     def fn(st, p, i):
+        st.device_exchange = device_exchange
         m = st.eng.to_device(mom[i])
         p2, m2 = st.step(p, m, 0.3, 0.7)
         return p2.cpu().numpy(), m2.cpu().numpy()
@@ -174,3 +177,69 @@ def test_wrongly_sharded_particles_are_reported():
     res, _ = run_ranks(world, cfg, pos, fn)
     assert res[0][0] == "raised"                          # accel(): the rank that holds the stray particle
     assert res[0][1] == "raised" and res[1][1] == "raised"   # step(): the count is all-reduced in migrate()
+
+
+@pytest.mark.parametrize("n_in", [0, 30, 100, 170])
+def test_migrate_merge_kernels(n_in):
+    """nb_migrate_merge on one device: arrivals fill holes / are appended, and with more leavers than arrivals
+    the tail is compacted into the remaining holes — the surviving set is exactly (kept + arrived)."""
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    rs = np.random.RandomState(n_in)
+    n, n_holes, cap = 1000, 100, 256
+    pos, mom = rs.random_sample((n + cap, 3)), rs.normal(size=(n + cap, 3))
+    holes = rs.choice(n, n_holes, replace=False).astype(np.int32)
+    holes[:7] = np.arange(n - 7, n)[::-1]                      # some holes inside the tail region
+    holes = np.unique(holes)[rs.permutation(np.unique(holes).size)].astype(np.int32)
+    n_holes = holes.size
+    arr = rs.normal(size=(n_in, 6)) + 10.0
+    na = n_in // 3
+    dpos, dmom = eng.to_device(pos.copy()), eng.to_device(mom.copy())
+    new_n = eng.migrate_merge(dpos, dmom, n, eng.to_device(holes), n_holes, eng.to_device(arr[:na].copy()) if na else None,
+                              na, eng.to_device(arr[na:].copy()) if n_in - na else None, n_in - na)
+    assert new_n == n + n_in - n_holes
+    keep = np.setdiff1d(np.arange(n), holes)
+    want = np.vstack([np.hstack([pos[keep], mom[keep]]), arr])
+    got = np.hstack([dpos[:new_n].cpu().numpy(), dmom[:new_n].cpu().numpy()])
+    assert got.shape == want.shape
+    o1, o2 = np.lexsort(got.T[::-1]), np.lexsort(want.T[::-1])
+    assert np.array_equal(got[o1], want[o2])
+
+
+def test_halo_select_and_nan_rows_in_the_cell_sort():
+    """nb_halo_select packs the face particles into fixed-capacity NaN-padded buffers; nb_cell_sort skips the NaN
+    rows, so (own + padded halo buffers) sorts exactly like (own + selected rows)."""
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    rs = np.random.RandomState(2)
+    L, n, cap, ncs = 100.0, 5000, 1024, 8
+    pos = rs.random_sample((n, 3)) * L
+    lo_edge, hi_edge = 7.5, 92.0
+    d = eng.to_device(pos)
+    out = torch.empty((2, cap, 3), dtype=torch.float64, device=eng.device)
+    cnt = torch.zeros(2, dtype=torch.int32, device=eng.device)
+    eng.halo_select(d, lo_edge, hi_edge, out[0], out[1], cnt)
+    c = cnt.cpu().numpy()
+    sel_lo, sel_hi = pos[pos[:, 0] < lo_edge], pos[pos[:, 0] >= hi_edge]
+    assert c[0] == sel_lo.shape[0] and c[1] == sel_hi.shape[0] and c.max() < cap
+    for b, want in ((0, sel_lo), (1, sel_hi)):
+        got = out[b].cpu().numpy()
+        assert np.isnan(got[c[b]:]).all()
+        g = got[:c[b]]
+        assert np.array_equal(g[np.lexsort(g.T[::-1])], want[np.lexsort(want.T[::-1])])
+    both = torch.cat([d, out[0], out[1]])
+    s4, perm, cs = eng.cell_sort(both, L, ncs)
+    ref4, refperm, refcs = eng.cell_sort(eng.to_device(np.vstack([pos, sel_lo, sel_hi])), L, ncs)
+    assert np.array_equal(cs.cpu().numpy(), refcs.cpu().numpy())
+    nv = int(cs[-1].item())
+    assert nv == n + c.sum()
+    # same multiset of cell-relative coordinates per cell
+    a, b = s4[:nv].cpu().numpy(), ref4[:nv].cpu().numpy()
+    csn = cs.cpu().numpy()
+    for cell in rs.randint(0, ncs ** 3, 40):
+        x, y = a[csn[cell]:csn[cell + 1]], b[csn[cell]:csn[cell + 1]]
+        assert np.array_equal(x[np.lexsort(x.T[::-1])], y[np.lexsort(y.T[::-1])])
+    # a buffer that is too small: the count still tells
+    small = torch.empty((2, 16, 3), dtype=torch.float64, device=eng.device)
+    eng.halo_select(d, lo_edge, hi_edge, small[0], small[1], cnt)
+    assert cnt.cpu().numpy()[0] == sel_lo.shape[0] > 16
