@@ -391,11 +391,12 @@ class DistForceStepper:
             raise ValueError(f"unknown force method {cfg.method!r}")
         self._acc = None
         self._pbuf = self._mbuf = None          # capacity buffers: rows [0,n) own particles, then halo / arrivals
-        self._hbuf = self._hcounts = self._hover = None
+        self._hbuf = self._hcounts = self._hover = self._n_mean = None
         self._mig = None
         # device-side halo selection / migration (nb_halo_select, nb_migrate_*): one host sync per step;
         # False keeps the eager torch exchange (reference implementation of the same bookkeeping, tests)
         self.device_exchange = True
+        self.halo_cap_floor = 4096
         self.mesh = None
         self._mark = lambda name, fn: fn()      # bench.py installs a CUDA-event recorder per step
         if cfg.method in ("pm", "p3m"):
@@ -415,9 +416,18 @@ class DistForceStepper:
         return self._acc[:n]
 
     def _halo_cap(self, n):
-        """Rows of one halo buffer: twice the uniform-density expectation n r_cut / slab width."""
+        """Rows of one halo buffer: twice the uniform-density expectation (N_total / ranks) r_cut / slab width.
+        The SAME number on every rank (the neighbours exchange the buffers at this fixed size), hence from the
+        global particle count, not from this rank's n."""
         c, lay = self.cfg, self.mesh.lay
-        return max(4096, int(2.0 * n * c.r_cut / (lay.nxl * c.cell)) + 1024)
+        if self._n_mean is None:
+            if c.npart:
+                self._n_mean = c.npart / self.world
+            else:       # unknown total: agree on the largest shard once
+                t = torch.tensor([n], dtype=torch.int64, device=self.eng.device)
+                self.comm.all_reduce(t, "max")
+                self._n_mean = float(t.item())
+        return max(self.halo_cap_floor, int(2.0 * self._n_mean * c.r_cut / (lay.nxl * c.cell)) + self.halo_cap_floor // 4)
 
     def _mig_cap(self, n):
         return max(4096, n // 8)

@@ -92,6 +92,7 @@ def test_sharded_step_with_migration(method, world, device_exchange):
 
     def fn(st, p, i):
         st.device_exchange = device_exchange
+        st.halo_cap_floor = 64          # the capacity formula (identical on all ranks) decides, not the floor
         m = st.eng.to_device(mom[i])
         p2, m2 = st.step(p, m, 0.3, 0.7)
         return p2.cpu().numpy(), m2.cpu().numpy()
