@@ -392,7 +392,7 @@ class DistForceStepper:
         self._acc = None
         self._pbuf = self._mbuf = None          # capacity buffers: rows [0,n) own particles, then halo / arrivals
         self._hbuf = self._hcounts = self._hover = self._n_mean = None
-        self._mig = None
+        self._mig = self._owner_buf = None
         # device-side halo selection / migration (nb_halo_select, nb_migrate_*): one host sync per step;
         # False keeps the eager torch exchange (reference implementation of the same bookkeeping, tests)
         self.device_exchange = True
@@ -432,11 +432,16 @@ class DistForceStepper:
     def _mig_cap(self, n):
         return max(4096, n // 8)
 
+    def _mig_rows(self, n):
+        """Rows reserved behind the own particles for arrivals (sticky like the buffers themselves)."""
+        return self._mig["cap"] if self._mig is not None and self._mig["cap"] >= self._mig_cap(n) else \
+            self._mig_cap(n) + self._mig_cap(n) // 4
+
     def _extra_rows(self, n):
         """Rows behind the own particles: both received halo buffers (P3M) or the arrivals of a migration."""
         if self.world == 1 or self.mesh is None:
             return 0
-        return max(2 * self._halo_cap(n) if self.cfg.method == "p3m" else 0, 2 * self._mig_cap(n))
+        return max(2 * self._halo_cap(n) if self.cfg.method == "p3m" else 0, 2 * self._mig_rows(n))
 
     def _own(self, pos, mom=None):
         """pos / mom as views (rows [0,n)) of this stepper's capacity buffers.  Halo copies and
@@ -616,6 +621,10 @@ class DistForceStepper:
             eng, dev = self.eng, self.eng.device
             pos, mom = self._own(pos, mom)
             cap = self._mig_cap(n)
+            if self._mig is not None and self._mig["cap"] >= cap:
+                cap = self._mig["cap"]          # sticky: n changes every step, a re-allocation costs a cudaMalloc stall
+            else:
+                cap += cap // 4
             if self._mig is None or self._mig["cap"] != cap:
                 self._mig = {"cap": cap, "send": torch.empty((2, cap, 6), dtype=torch.float64, device=dev),
                              "recv": torch.empty((2, cap, 6), dtype=torch.float64, device=dev),
@@ -624,7 +633,10 @@ class DistForceStepper:
                              "rc": torch.zeros(2, dtype=torch.int32, device=dev)}
             mg = self._mig
             prev, nxt = (self.rank - 1) % self.world, (self.rank + 1) % self.world
-            owner, _ = eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world, want_counts=False)
+            if self._owner_buf is None or self._owner_buf.shape[0] < self._pbuf.shape[0]:
+                self._owner_buf = torch.empty(self._pbuf.shape[0], dtype=torch.int32, device=dev)
+            owner, _ = eng.slab_owner(pos, c.cell, c.gridsize, lay.nxl, self.world, want_counts=False,
+                                      out=self._owner_buf)
             eng.migrate_split(pos, mom, owner, self.rank, prev, nxt, mg["send"][0], mg["send"][1], mg["holes"],
                               mg["counts"])
             # my "to previous" count -> previous rank, I receive the next rank's (its particles coming down to me)

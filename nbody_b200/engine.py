@@ -578,9 +578,10 @@ class Engine:
         _lib.check(self.lib.nb_slab_unpack(self.ctx, _ptr(src), _ptr(dst), int(nxl), int(G), int(nyl), int(nzh),
                                            self.stream), "nb_slab_unpack")
 
-    def slab_owner(self, pos, cell, N, planes_per_rank, G, want_counts=True):
+    def slab_owner(self, pos, cell, N, planes_per_rank, G, want_counts=True, out=None):
         self._check_pos(pos)
-        owner = torch.empty(pos.shape[0], dtype=torch.int32, device=self.device)
+        owner = out[:pos.shape[0]] if out is not None else torch.empty(pos.shape[0], dtype=torch.int32,
+                                                                      device=self.device)
         counts = torch.empty(G, dtype=torch.int64, device=self.device) if want_counts else None
         _lib.check(self.lib.nb_slab_owner(self.ctx, _ptr(pos), pos.shape[0], float(cell), int(N),
                                           int(planes_per_rank), _ptr(owner), _ptr(counts), int(G), self.stream),
