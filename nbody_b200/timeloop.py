@@ -158,22 +158,54 @@ def evolve_subcycled(stepper, cosmo: Cosmology, pos, mom, a_edges, output_at=(),
 
 
 class PeriodicPP:
-    """Adapter for a `pp` ForceStepper inside the comoving loop: the box is periodic, so every step
-    uses the nearest-image force plus the Ewald correction table (CONCEPT's periodic PP gravity)."""
+    """Adapter for a `pp` ForceStepper inside the comoving loop: the box is periodic (CONCEPT's PP gravity
+    is the Ewald sum), so every force evaluation is the periodic one.  Two evaluations of the same force:
 
-    def __init__(self, stepper, ewald_gridsize=64):
+    mode="ewald"  direct: softened nearest-image pair sum + tabulated Ewald correction (nb_pp_accel_ewald),
+                  O(N²) at 45 G pairs/s;
+    mode="pme"    particle-mesh Ewald: the reciprocal-space sum through the PM mesh and the real-space erfc
+                  sum through the cell-list pair kernel — the P³M machinery with accuracy parameters instead
+                  of CONCEPT's production ones: mesh `pme_mesh` (default 4 cbrt(N)), split scale
+                  `pme_rs_cells` = 3 mesh cells, real-space range 6.5 r_s (the dropped tail is 1e-4 of a pair
+                  term at r_cut).  Measured against the direct Ewald sum in tests/test_gpu_ewald.py."""
+
+    def __init__(self, stepper, ewald_gridsize=64, mode="ewald", pme_mesh=None, pme_rs_cells=3.0,
+                 pme_rcut_over_rs=6.5):
         self.stepper = stepper
         self.cfg = stepper.cfg
+        self.mode = mode
         stepper.ewald_gridsize = int(ewald_gridsize)
+        if mode == "pme":
+            import copy
+            from . import force as F
+            c = copy.copy(stepper.cfg)
+            n = round(c.npart ** (1.0 / 3.0))
+            c.method, c.gridsize = "p3m", int(pme_mesh or 4 * n)
+            c.interlace, c.deconvolve = (True, True), (True, True)
+            c.r_s_cells, c.r_cut_over_rs = float(pme_rs_cells), float(pme_rcut_over_rs)
+            if c.boxsize < 3.0 * c.r_cut:
+                raise ValueError("particle-mesh Ewald needs boxsize >= 3 r_cut: use a finer pme_mesh")
+            self.pme = F.ForceStepper(c, stepper.eng)
+        elif mode != "ewald":
+            raise ValueError("mode must be 'ewald' or 'pme'")
+
+    def accel(self, pos):
+        if self.mode == "pme":
+            return self.pme.accel(pos)
+        return self.stepper.accel(pos, periodic_pp="ewald")
 
     def step(self, pos, mom, dt_kick, dt_drift):
+        if self.mode == "pme":
+            return self.pme.step(pos, mom, dt_kick, dt_drift)
         return self.stepper.step(pos, mom, dt_kick, dt_drift, periodic_pp="ewald")
 
-    # sub-cycled loop: the whole PP force is "short range"
+    # sub-cycled loop: the whole PP force is "short range" for the direct sum; the PME form splits like P3M
     def accel_long(self, pos):
-        return None
+        return self.pme.accel_long(pos) if self.mode == "pme" else None
 
     def accel_short(self, pos):
+        if self.mode == "pme":
+            return self.pme.accel_short(pos)
         return self.stepper.accel(pos, periodic_pp="ewald")
 
     def kick(self, pos, mom, acc, k):
@@ -284,7 +316,8 @@ def zeldovich_ics(cosmo: Cosmology, L, n, a_begin, mass, A_s=2.1e-9, n_s=0.9649,
 
 
 def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_max=0.025, output_dir=None,
-             engine=None, overrides=None, subcycle=True, eta=0.025, max_sub=32, linear_power=None, lattice_offset=0.0):
+             engine=None, overrides=None, subcycle=True, eta=0.025, max_sub=32, linear_power=None, lattice_offset=0.0,
+             periodic_pp="ewald"):
     """Run a CONCEPT-style `.param` file (path, text or loaded dict): ICs at a_begin, leapfrog to
     every `output_times['snapshot']` entry.  Returns [(a, pos, mom)] as host float64 arrays; with
     `output_dir` each output is also written as `snapshot_a=%.2f.hdf5` in CONCEPT's layout."""
@@ -312,7 +345,7 @@ def simulate(param, output_times=None, mesh=None, method=None, seed=None, dlna_m
     cfg.a = 1.0
     stepper = F.ForceStepper(cfg, eng)
     if cfg.method == "pp":
-        stepper = PeriodicPP(stepper)
+        stepper = PeriodicPP(stepper, mode=periodic_pp)
     lpt = int((vals.get("realization_options") or {}).get("LPT", 1))
     pos, mom = zeldovich_ics(cosmo, cfg.boxsize, n, cfg.a_begin, cfg.mass, A_s=float(prim.get("A_s", 2.1e-9)),
                              n_s=float(prim.get("n_s", 0.9649)), seed=seed, engine=eng, lpt=lpt,
