@@ -353,7 +353,11 @@ def write_snapshot(filename, pos, mom, boxsize, a=1.0, mass=1.0, H0=None, Omega_
     `unit length/time/mass`; group components/matter with attributes N, mass, species and the
     (Np,3) float64 datasets pos and mom.  read_positions / read_momenta / read_boxsize / read_attrs
     read it back (h5py is not in this image; the layout follows the HDF5 1.x file-format
-    specification for superblock v0, see the reader)."""
+    specification for superblock v0, see the reader).
+    UNVALIDATED AGAINST libhdf5: no HDF5 library has opened one of these files yet.  Known departures from
+    the files CONCEPT writes: fixed-length instead of variable-length strings, non-ASCII attribute names
+    ('Ωb', 'Ωcdm') in version-1 attribute messages without a character-set field, no modification-time / NIL
+    messages.  A consumer that reads through h5py should be checked once against a file written here."""
     pos = np.ascontiguousarray(pos, dtype=np.float64)
     mom = np.ascontiguousarray(mom, dtype=np.float64)
     if pos.ndim != 2 or pos.shape[1] != 3 or mom.shape != pos.shape:
