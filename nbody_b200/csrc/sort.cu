@@ -42,27 +42,18 @@ sort_count_kernel(const double* __restrict__ pos, int64_t np, double L, double c
   }
 }
 
-// Slot of a particle = cell_start[c] + its rank among the particles of cell c.  The rank comes from a
-// returning atomic on the cell's fill counter; spatially coherent input (lattice order) puts several lanes
-// of a warp into the same cell, so the lanes are grouped by cell (match.any) and ONE atomic per group
-// reserves a run of slots (ncu, C5: one atomic per lane kept the kernel at 6.7 % issue activity, 4.4 ms).
+// (A warp-aggregated variant — match.any on the cell id, one returning atomic per (warp, cell) group — measured
+// 5.21 ms against 5.04 ms for the whole sort at C5: the kernel is bound by its scattered 16-byte stores, not by
+// the atomics.)
 __global__ void __launch_bounds__(256)
 sort_scatter_kernel(const double* __restrict__ pos, int64_t np, double L, double cs, double inv_cs, int ncs,
                     float mass, const int* __restrict__ cell_of, const int* __restrict__ cell_start,
                     int* __restrict__ fill, float4* __restrict__ sorted, int* __restrict__ perm) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t nround = (np + stride - 1) / stride;
-  const int lane = threadIdx.x & 31;
-  for (int64_t r = 0; r < nround; ++r) {                      // whole warps stay in the loop (match.any)
-    const int64_t p = r * stride + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int c = p < np ? cell_of[p] : -1;
-    const unsigned grp = __match_any_sync(0xffffffffu, c);
-    if (c < 0) continue;                                       // padding lane or NaN row
-    const int leader = __ffs(grp) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(&fill[c], __popc(grp));
-    base = __shfl_sync(grp, base, leader);
-    const int slot = cell_start[c] + base + __popc(grp & ((1u << lane) - 1u));
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < np; p += stride) {
+    const int c = cell_of[p];
+    if (c < 0) continue;
+    const int slot = cell_start[c] + atomicAdd(&fill[c], 1);
     double rx, ry, rz;
     sort_cell_coord(pos[3 * p], L, inv_cs, ncs, &rx, cs);
     sort_cell_coord(pos[3 * p + 1], L, inv_cs, ncs, &ry, cs);
