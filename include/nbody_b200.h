@@ -280,6 +280,10 @@ int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start
  * below the kernel's natural residency (4) leaves shared memory / registers on every SM for
  * kernels of another stream (the PM chain of the same step runs concurrently). */
 int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm);
+/* sm_limit > 0: the next nb_p3m_short calls run the pair kernel as a persistent grid confined to the SMs
+ * [0, sm_limit) (CTAs on other SMs exit at once, work units come from an atomic counter), so that the
+ * memory-bound mesh chain of the same step can run beside it on the remaining SMs (another stream).  0 = off. */
+int nb_p3m_set_sm_limit(nb_ctx* ctx, int sm_limit);
 /* Pair statistics of the same traversal: out2[0] = candidate pairs (all j in the 27
  * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]).
  * perm / i_limit as in nb_p3m_short (perm may be NULL when i_limit = 0). */

@@ -71,6 +71,7 @@ struct nb_ctx {
   int num_sms = NB_NUM_SMS_FALLBACK;
   int64_t launches = 0;
   int p3m_ctas_per_sm = 0;   // nb_p3m_set_ctas_per_sm
+  int p3m_sm_limit = 0;      // nb_p3m_set_sm_limit: pair kernel confined to the first SMs (overlapped step)
   void* scratch[NB_SCR_NSLOTS] = {};
   size_t scratch_bytes[NB_SCR_NSLOTS] = {};
   // key: (cufftType, n0, n1, n2, batch, layout) ; layout 0 = plain 3-D

@@ -477,7 +477,17 @@ __global__ void __launch_bounds__(P3M6_WARPS * 32, CTAS)
 p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
-                    int* __restrict__ overflow_list, int* __restrict__ overflow_count) {
+                    int* __restrict__ overflow_list, int* __restrict__ overflow_count,
+                    int* __restrict__ unit_counter = nullptr, int sm_limit = 0) {
+  // SM partition for the overlapped P3M step (nb_p3m_set_sm_limit): CTAs that land on an SM >= sm_limit leave
+  // at once, the others pull their work units from an atomic counter — the pair kernel then occupies the first
+  // sm_limit SMs completely (6 CTAs fill their shared memory) and the memory-bound mesh chain of the same step,
+  // launched on another stream, gets the remaining SMs to itself.
+  if (sm_limit > 0) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if ((int)smid >= sm_limit) return;
+  }
   extern __shared__ __align__(16) unsigned char p3m6_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int li = lane & 7, strm = lane >> 3;
@@ -507,7 +517,14 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
   const int64_t col_lo = cell_lo / ncs, col_hi = (cell_hi + ncs - 1) / ncs;
   const int64_t nunits = (col_hi - col_lo) * nrun;
-  for (int64_t u = blockIdx.x; u < nunits; u += gridDim.x) {
+  for (int64_t u = blockIdx.x;; u += gridDim.x) {
+    if (unit_counter) {      // dynamic: one unit per fetch (s_tot[2] is not used by the tile code)
+      __syncthreads();
+      if (threadIdx.x == 0) s_tot[2] = atomicAdd(unit_counter, 1);
+      __syncthreads();
+      u = s_tot[2];
+    }
+    if (u >= nunits) break;
     const int64_t col = col_lo + u / nrun;
     const int z0 = (int)(u % nrun) * P3M6_WARPS;
     const int cx = (int)(col / ncs), cy = (int)(col % ncs);
@@ -631,6 +648,12 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+extern "C" int nb_p3m_set_sm_limit(nb_ctx* ctx, int sm_limit) {
+  NB_REQUIRE(ctx && sm_limit >= 0, "bad arguments");
+  ctx->p3m_sm_limit = sm_limit >= ctx->num_sms ? 0 : sm_limit;
+  return NB_OK;
+}
+
 extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
   NB_REQUIRE(ctx && ctas_per_sm >= 0 && ctas_per_sm <= 64, "ctas_per_sm must be in [0, 64]");
   ctx->p3m_ctas_per_sm = ctas_per_sm;
@@ -678,12 +701,18 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     NB_CHECK_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int), st));
     const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
     const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nrun;
-    const int64_t nblk = nunits < cap ? nunits : cap;
+    int64_t nblk = nunits < cap ? nunits : cap;
+    int* unit_counter = nullptr;
+    if (ctx->p3m_sm_limit > 0) {      // SM-partitioned persistent form: every resident slot gets a CTA
+      unit_counter = ovf_count + 1;
+      NB_CHECK_CUDA(cudaMemsetAsync(unit_counter, 0, sizeof(int), st));
+      nblk = (int64_t)ctx->num_sms * 6;
+    }
     NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<QD6, 6, false, CAP6>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem6));
     p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
         (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, CAP6,
-        ovf_list, ovf_count);
+        ovf_list, ovf_count, unit_counter, ctx->p3m_sm_limit);
     NB_LAUNCHED(ctx);
     const int tile_cap = P3M4_CAP;
     const size_t smem4 = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, 64);

@@ -368,6 +368,9 @@ class Engine:
             int(n_ghost), float(cell), _ptr(pos), _ptr(mom), _ptr(acc_add), _ptr(acc_out), pos.shape[0],
             float(gscale), float(kick), float(drift), float(L), self.stream), "nb_gather_kick_drift_add")
 
+    def p3m_set_sm_limit(self, n: int):
+        _lib.check(self.lib.nb_p3m_set_sm_limit(self.ctx, int(n)), "nb_p3m_set_sm_limit")
+
     def p3m_set_ctas_per_sm(self, n: int):
         _lib.check(self.lib.nb_p3m_set_ctas_per_sm(self.ctx, int(n)), "nb_p3m_set_ctas_per_sm")
 

@@ -50,6 +50,7 @@ class ForceStepper:
         self.fused_tail = cfg.method == "p3m"
         self.overlap = cfg.method == "p3m" and os.environ.get("NB_P3M_OVERLAP", "0") == "1"
         self.p3m_ctas = int(os.environ.get("NB_P3M_CTAS", "4"))
+        self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "96"))
         self._acc_s = None
         self._streams = None
 
@@ -143,14 +144,16 @@ class ForceStepper:
             pm_stream, sr_stream = self._streams
             pm_stream.wait_stream(main)
             sr_stream.wait_stream(main)
-            eng.p3m_set_ctas_per_sm(self.p3m_ctas)
+            # the pair kernel takes the first `p3m_sms` SMs for itself (persistent grid, CTAs elsewhere exit),
+            # the memory-bound mesh chain runs on the others: FP32-bound and HBM-bound halves of the step side by side
+            eng.p3m_set_sm_limit(self.p3m_sms)
             try:
                 with torch.cuda.stream(sr_stream):
                     self.short_range(pos, self._acc_s, accumulate=False)
                 with torch.cuda.stream(pm_stream):
                     f, fs = self.pm_mesh(pos)
             finally:
-                eng.p3m_set_ctas_per_sm(0)
+                eng.p3m_set_sm_limit(0)
             main.wait_stream(pm_stream)
             main.wait_stream(sr_stream)
         else:
