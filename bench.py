@@ -458,6 +458,12 @@ def run_ours(args):
         line["phase_ms_note"] = ("phases timed in a separate sequential pass (one stream); the timed step is "
                                  "ForceStepper.step" + (" (short range into its own buffer, mesh chain, one fused "
                                                         "gather + kick + drift tail)" if method == "p3m" else ""))
+        ov = getattr(stepper, "overlap", False)
+        if method == "p3m" and (ov is True or (ov == "auto" and n ** 3 >= stepper.overlap_min_particles)):
+            line["phase_ms_note"] += (f"; in the timed step the pair kernel (persistent, first {stepper.p3m_sms} SMs) and "
+                                      "the mesh chain (other SMs) run side by side after the cell sort, so ms_per_step "
+                                      "is less than the sum of the phases")
+            line["overlap"] = {"pair_kernel_sms": stepper.p3m_sms, "sequential_sum_ms": round(sum(phase_ms.values()), 3)}
     if phase_by_rank is not None:
         line["phase_ms_by_rank"] = phase_by_rank
     if invariants is not None:

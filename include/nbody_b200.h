@@ -284,6 +284,12 @@ int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm);
  * [0, sm_limit) (CTAs on other SMs exit at once, work units come from an atomic counter), so that the
  * memory-bound mesh chain of the same step can run beside it on the remaining SMs (another stream).  0 = off. */
 int nb_p3m_set_sm_limit(nb_ctx* ctx, int sm_limit);
+/* Raises the stop flag of the confined pair kernel from `stream` (the mesh-chain stream, after its last kernel):
+ * the confined CTAs stop fetching units and the unconfined second launch of nb_p3m_short finishes the list. */
+int nb_p3m_mesh_done(nb_ctx* ctx, void* stream);
+/* One thread spinning for about `us` microseconds on `stream` (head of the mesh-chain stream of the overlapped
+ * P3M step: the persistent pair kernel launched beside it gets its CTAs resident first). */
+int nb_delay_us(nb_ctx* ctx, int us, void* stream);
 /* Pair statistics of the same traversal: out2[0] = candidate pairs (all j in the 27
  * neighbour cells of every i), out2[1] = pairs with 0 < r < r_cut (device int64[2]).
  * perm / i_limit as in nb_p3m_short (perm may be NULL when i_limit = 0). */

@@ -57,6 +57,8 @@ PROTOTYPES = {
                              c_f64, c_f64, c_i32, c_i64, c_vp, c_vp]),
     "nb_p3m_set_ctas_per_sm": (c_i32, [c_vp, c_i32]),
     "nb_p3m_set_sm_limit": (c_i32, [c_vp, c_i32]),
+    "nb_delay_us": (c_i32, [c_vp, c_i32, c_vp]),
+    "nb_p3m_mesh_done": (c_i32, [c_vp, c_vp]),
     "nb_p3m_count_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i64, c_i64, c_f64, c_f64, c_vp, c_vp]),
     "nb_cic_deposit_slab": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_i32, c_i32, c_i32, c_vp, c_f64, c_i32, c_vp,
                                     c_vp]),

@@ -478,11 +478,14 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
                     int* __restrict__ overflow_list, int* __restrict__ overflow_count,
-                    int* __restrict__ unit_counter = nullptr, int sm_limit = 0) {
+                    int* __restrict__ unit_counter = nullptr, int sm_limit = 0,
+                    const int* __restrict__ stop_flag = nullptr) {
   // SM partition for the overlapped P3M step (nb_p3m_set_sm_limit): CTAs that land on an SM >= sm_limit leave
   // at once, the others pull their work units from an atomic counter — the pair kernel then occupies the first
   // sm_limit SMs completely (6 CTAs fill their shared memory) and the memory-bound mesh chain of the same step,
-  // launched on another stream, gets the remaining SMs to itself.
+  // launched on another stream, gets the remaining SMs to itself.  When the mesh chain is done it raises
+  // *stop_flag (nb_p3m_mesh_done): the confined CTAs stop fetching and a second, unconfined launch on the same
+  // counter finishes the units on the whole GPU.
   if (sm_limit > 0) {
     unsigned smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -520,7 +523,8 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   for (int64_t u = blockIdx.x;; u += gridDim.x) {
     if (unit_counter) {      // dynamic: one unit per fetch (s_tot[2] is not used by the tile code)
       __syncthreads();
-      if (threadIdx.x == 0) s_tot[2] = atomicAdd(unit_counter, 1);
+      if (threadIdx.x == 0)
+        s_tot[2] = (stop_flag && *(const volatile int*)stop_flag) ? 0x7fffffff : atomicAdd(unit_counter, 1);
       __syncthreads();
       u = s_tot[2];
     }
@@ -648,6 +652,16 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
   }
 }
 
+extern "C" int nb_p3m_mesh_done(nb_ctx* ctx, void* stream) {
+  NB_REQUIRE(ctx, "bad arguments");
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  void* fl = nullptr;
+  int rc = nb_scratch(ctx, NB_SCR_FLAGS, 64, &fl);
+  if (rc) return rc;
+  NB_CHECK_CUDA(cudaMemsetAsync((int*)fl + 1, 1, sizeof(int), (cudaStream_t)stream));
+  return NB_OK;
+}
+
 extern "C" int nb_p3m_set_sm_limit(nb_ctx* ctx, int sm_limit) {
   NB_REQUIRE(ctx && sm_limit >= 0, "bad arguments");
   ctx->p3m_sm_limit = sm_limit >= ctx->num_sms ? 0 : sm_limit;
@@ -704,16 +718,28 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     int64_t nblk = nunits < cap ? nunits : cap;
     int* unit_counter = nullptr;
     if (ctx->p3m_sm_limit > 0) {      // SM-partitioned persistent form: every resident slot gets a CTA
-      unit_counter = ovf_count + 1;
-      NB_CHECK_CUDA(cudaMemsetAsync(unit_counter, 0, sizeof(int), st));
+      void* fl = nullptr;
+      rc = nb_scratch(ctx, NB_SCR_FLAGS, 64, &fl);
+      if (rc) return rc;
+      unit_counter = (int*)fl;        // [0] unit counter, [1] stop flag (nb_p3m_mesh_done)
+      NB_CHECK_CUDA(cudaMemsetAsync(unit_counter, 0, 2 * sizeof(int), st));
       nblk = (int64_t)ctx->num_sms * 6;
     }
     NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<QD6, 6, false, CAP6>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem6));
     p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
         (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, CAP6,
-        ovf_list, ovf_count, unit_counter, ctx->p3m_sm_limit);
+        ovf_list, ovf_count, unit_counter, ctx->p3m_sm_limit, unit_counter ? unit_counter + 1 : nullptr);
     NB_LAUNCHED(ctx);
+    if (unit_counter) {
+      // second, unconfined launch on the same counter: the units left when the mesh chain raised the stop flag —
+      // and every unit, should the confined launch have found the SMs busy and lost its CTAs (a CTA that exits
+      // on a foreign SM is not replaced).  Empty when the confined CTAs got through the list.
+      p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+          (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim,
+          CAP6, ovf_list, ovf_count, unit_counter, 0, nullptr);
+      NB_LAUNCHED(ctx);
+    }
     const int tile_cap = P3M4_CAP;
     const size_t smem4 = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, 64);
     NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -371,6 +371,12 @@ class Engine:
     def p3m_set_sm_limit(self, n: int):
         _lib.check(self.lib.nb_p3m_set_sm_limit(self.ctx, int(n)), "nb_p3m_set_sm_limit")
 
+    def p3m_mesh_done(self):
+        _lib.check(self.lib.nb_p3m_mesh_done(self.ctx, self.stream), "nb_p3m_mesh_done")
+
+    def delay_us(self, us: int):
+        _lib.check(self.lib.nb_delay_us(self.ctx, int(us), self.stream), "nb_delay_us")
+
     def p3m_set_ctas_per_sm(self, n: int):
         _lib.check(self.lib.nb_p3m_set_ctas_per_sm(self.ctx, int(n)), "nb_p3m_set_ctas_per_sm")
 

@@ -42,15 +42,18 @@ class ForceStepper:
             if self.ncs < 3:
                 raise ValueError("P3M short range needs boxsize >= 3 r_cut")
         # P3M: the short-range part goes into its own buffer and ONE fused tail kernel does
-        # gather(mesh) + short -> kick -> drift.  NB_P3M_OVERLAP=1 additionally runs the mesh chain
-        # and the pair kernel concurrently on two streams (pair-kernel grid held to NB_P3M_CTAS
-        # CTAs per SM).  Measured on B200 at config 5: 185-231 ms against 184 ms
-        # one after the other — the pair kernel is latency-bound and needs all of an SM's shared
-        # memory, cuFFT's 64 KB CTAs do not fit beside it — so the default is sequential.
+        # gather(mesh) + short -> kick -> drift.  At large N the pair kernel and the mesh chain run side by
+        # side on an SM partition: the pair kernel, a persistent grid confined to the first
+        # `p3m_sms` SMs, against the memory-bound mesh chain on the rest.  Measured on B200 at config 5:
+        # 140.4 ms per step at 88 of 148 SMs against 162.6 ms one after the other (80-104 SMs: 140-143 ms).
+        # NB_P3M_OVERLAP=0/1 forces it off/on; the default turns it on from 2^26 particles (the size it was
+        # measured at is 2^27; small steps are launch-bound and gain nothing from it).
         self.fused_tail = cfg.method == "p3m"
-        self.overlap = cfg.method == "p3m" and os.environ.get("NB_P3M_OVERLAP", "0") == "1"
-        self.p3m_ctas = int(os.environ.get("NB_P3M_CTAS", "4"))
-        self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "96"))
+        ov = os.environ.get("NB_P3M_OVERLAP", "auto")
+        self.overlap = cfg.method == "p3m" and (True if ov == "1" else "auto" if ov == "auto" else False)
+        self.overlap_min_particles = 1 << 26
+        self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "0"))      # 0: 0.595 x the device's SM count (88 of 148)
+        self.p3m_delay_us = int(os.environ.get("NB_P3M_DELAY_US", "40"))
         self._acc_s = None
         self._streams = None
 
@@ -131,29 +134,41 @@ class ForceStepper:
     def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None):
         """Cell sort + pair kernel into a separate buffer, mesh chain, then ONE fused kernel:
         g = gather(mesh) + short; acc_out <- g and/or kick + drift.  With self.overlap the two
-        parts run on two streams (mesh chain on a high-priority one)."""
+        parts run on two streams and two disjoint sets of SMs."""
         c, eng = self.cfg, self.eng
         dev = eng.device
         n = pos.shape[0]
         if self._acc_s is None or self._acc_s.shape[0] != n:
             self._acc_s = torch.empty((n, 3), dtype=torch.float64, device=dev)
         main = torch.cuda.current_stream(dev)
-        if self.overlap:
+        if self.overlap is True or (self.overlap == "auto" and n >= self.overlap_min_particles):
             if self._streams is None:
                 self._streams = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
+                if self.p3m_sms <= 0:
+                    self.p3m_sms = max(1, round(0.595 * torch.cuda.get_device_properties(dev).multi_processor_count))
             pm_stream, sr_stream = self._streams
-            pm_stream.wait_stream(main)
             sr_stream.wait_stream(main)
             # the pair kernel takes the first `p3m_sms` SMs for itself (persistent grid, CTAs elsewhere exit),
-            # the memory-bound mesh chain runs on the others: FP32-bound and HBM-bound halves of the step side by side
+            # the memory-bound mesh chain runs on the others: FP32-bound and HBM-bound halves of the step side by
+            # side.  The pair kernel must find the GPU idle when it starts (a CTA that exits on a foreign SM is not
+            # replaced): the cell sort runs alone, and the mesh stream starts with a short delay kernel.
             eng.p3m_set_sm_limit(self.p3m_sms)
             try:
                 with torch.cuda.stream(sr_stream):
-                    self.short_range(pos, self._acc_s, accumulate=False)
+                    sorted4, perm, cell_start = eng.cell_sort(pos, c.boxsize, self.ncs, mass=1.0)
+                    sorted_ev = torch.cuda.Event()
+                    sorted_ev.record(sr_stream)
+                    eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut, c.eps,
+                                  scale=c.G * c.mass, out=self._acc_s, accumulate=False)
+                pm_stream.wait_event(sorted_ev)
                 with torch.cuda.stream(pm_stream):
+                    eng.delay_us(self.p3m_delay_us)
                     f, fs = self.pm_mesh(pos)
+                    eng.p3m_mesh_done()
             finally:
                 eng.p3m_set_sm_limit(0)
+            for t in (sorted4, perm, cell_start):          # freed on this stream, used on sr_stream
+                t.record_stream(sr_stream)
             main.wait_stream(pm_stream)
             main.wait_stream(sr_stream)
         else:

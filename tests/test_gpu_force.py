@@ -93,6 +93,59 @@ def test_p3m_short_range_clustered_and_empty_cells(F):
     assert err(acc.cpu().numpy(), ref) <= TOL
 
 
+@pytest.mark.parametrize("busy", [False, True])
+def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
+    """The SM-partitioned form of the pair kernel (nb_p3m_set_sm_limit: persistent CTAs on the first SMs pull units
+    from a counter, an unconfined second launch takes what is left) gives the accelerations of the plain launch
+    (to the order of the float64 atomics) - also when the GPU is busy at launch time and the confined launch loses CTAs to foreign SMs, and when
+    the stop flag is already up (nb_p3m_mesh_done before the launch resets it)."""
+    import torch
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    L, N, n = 100.0, 64, 40
+    pos = zeldovich_particles(n, L, seed=11)
+    cfg = cfg_for("p3m", n, N, L)
+    st = F.ForceStepper(cfg, eng)
+    dpos = eng.to_device(pos)
+    plain = st.short_range(dpos, eng.to_device(np.zeros_like(pos)), accumulate=False).cpu().numpy()
+    eng.p3m_set_sm_limit(24)
+    try:
+        eng.p3m_mesh_done()
+        if busy:
+            side = torch.cuda.Stream(device=eng.device)
+            with torch.cuda.stream(side):
+                eng.delay_us(3000)
+                big = torch.empty(1 << 28, dtype=torch.float32, device=eng.device)
+                for _ in range(4):
+                    big.add_(1.0)
+        conf = st.short_range(dpos, eng.to_device(np.zeros_like(pos)), accumulate=False).cpu().numpy()
+        torch.cuda.synchronize()
+    finally:
+        eng.p3m_set_sm_limit(0)
+    # the same pair terms; float64 atomics across tiles land in a different order
+    assert err(conf, plain) <= 1e-6
+
+
+def test_p3m_step_overlapped_equals_sequential(F, monkeypatch):
+    """ForceStepper.step with the pair kernel and the mesh chain side by side (NB_P3M_OVERLAP=1) against the
+    sequential step: same positions and momenta."""
+    from nbody_b200.engine import default_engine
+    eng = default_engine()
+    L, N, n = 100.0, 64, 32
+    pos = zeldovich_particles(n, L, seed=12)
+    out = []
+    for ov in ("0", "1"):
+        monkeypatch.setenv("NB_P3M_OVERLAP", ov)
+        st = F.ForceStepper(cfg_for("p3m", n, N, L), eng)
+        assert st.overlap is (ov == "1")
+        p, m = eng.to_device(pos), eng.to_device(np.zeros_like(pos))
+        for _ in range(3):
+            st.step(p, m, 0.01, 0.01)
+        out.append((p.cpu().numpy(), m.cpu().numpy()))
+    assert np.abs(out[0][0] - out[1][0]).max() <= 1e-9 * L
+    assert err(out[1][1], out[0][1]) <= 1e-6
+
+
 @pytest.mark.parametrize("method", ["pm", "p3m", "pp"])
 def test_force_step_kick_drift(F, method):
     L, n, N = 500.0, 12, 24
