@@ -21,6 +21,7 @@ parity-tested on a single GPU before it is run on several.
 from __future__ import annotations
 
 import math
+import os
 import threading
 
 import numpy as np
@@ -399,6 +400,16 @@ class DistForceStepper:
         self.halo_cap_floor = 4096
         self.mesh = None
         self._mark = lambda name, fn: fn()      # bench.py installs a CUDA-event recorder per step
+        # pair kernel beside the mesh chain on an SM partition (force.py / DESIGN.md 8.2): the confined pair kernel
+        # runs on a side stream, the mesh chain and its transposes stay on the caller's stream.  Half of the SMs by
+        # default: per rank the mesh chain (with its all-to-all) is the longer half, and whichever side finishes
+        # first hands its SMs to the other (stop flag + unconfined second launch / retiring CTAs).
+        ov = os.environ.get("NB_P3M_OVERLAP", "auto")
+        self.overlap = cfg.method == "p3m" and (True if ov == "1" else "auto" if ov == "auto" else False)
+        self.overlap_min_particles = 1 << 23          # own particles of the rank
+        self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "0"))
+        self.p3m_delay_us = int(os.environ.get("NB_P3M_DELAY_US", "40"))
+        self._sr_stream = None
         if cfg.method in ("pm", "p3m"):
             self.nb = 2 if cfg.interlace[0] else 1
             self.nc = 6 if cfg.interlace[1] else 3
@@ -532,7 +543,8 @@ class DistForceStepper:
         self.comm.shift(self._hbuf[1], dst[cap:], +1)       # my high face -> next slab; I receive the previous slab's
         return self._pbuf[:n + 2 * cap]
 
-    def short_range(self, pos, acc, accumulate=True):
+    def _short_prepare(self, pos):
+        """Halo exchange + cell sort of own and halo particles; returns what the pair kernel needs."""
         c, mk = self.cfg, self._mark
         n = pos.shape[0]
         if self.world > 1 and self.device_exchange:
@@ -555,14 +567,49 @@ class DistForceStepper:
         cx_lo = max(0, int(math.floor(lay.x0 * c.cell / cs)) - 1)
         cx_hi = min(self.ncs, int(math.floor((lay.x0 + lay.nxl) * c.cell / cs)) + 2)
         plane = self.ncs * self.ncs
-        mk("p3m_short", lambda: self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut,
-                                                   c.eps, scale=c.G * c.mass, out=acc, accumulate=accumulate,
-                                                   cell_lo=cx_lo * plane, cell_hi=cx_hi * plane,
-                                                   i_limit=pos.shape[0]))
         self.last_sorted = (sorted4, cell_start)
+        return sorted4, perm, cell_start, cx_lo * plane, cx_hi * plane, n
+
+    def _short_pairs(self, prep, acc, accumulate):
+        c = self.cfg
+        sorted4, perm, cell_start, cell_lo, cell_hi, n = prep
+        return self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut, c.eps,
+                                  scale=c.G * c.mass, out=acc, accumulate=accumulate, cell_lo=cell_lo, cell_hi=cell_hi,
+                                  i_limit=n)
+
+    def short_range(self, pos, acc, accumulate=True):
+        prep = self._short_prepare(pos)
+        self._mark("p3m_short", lambda: self._short_pairs(prep, acc, accumulate))
         return acc
 
-    # -- PP ---------------------------------------------------------------------------------------
+    def _short_and_mesh_side_by_side(self, pos, acc_s):
+        """P3M step, overlapped form: halo exchange and cell sort alone, then the pair kernel confined to the first
+        p3m_sms SMs on a side stream while the mesh chain (deposit, slab FFTs with their transposes, k-space
+        kernel) runs on the caller's stream on the other SMs.  Returns the force meshes."""
+        eng, mk = self.eng, self._mark
+        dev = eng.device
+        main = torch.cuda.current_stream(dev)
+        if self._sr_stream is None:
+            self._sr_stream = torch.cuda.Stream(device=dev)
+            if self.p3m_sms <= 0:
+                self.p3m_sms = max(1, torch.cuda.get_device_properties(dev).multi_processor_count // 2)
+        sr = self._sr_stream
+        prep = self._short_prepare(pos)
+        sr.wait_stream(main)
+        eng.p3m_set_sm_limit(self.p3m_sms)
+        try:
+            with torch.cuda.stream(sr):
+                mk("p3m_short(side stream, confined)", lambda: self._short_pairs(prep, acc_s, False))
+        finally:
+            eng.p3m_set_sm_limit(0)
+        for t in prep[:3]:
+            t.record_stream(sr)
+        eng.delay_us(self.p3m_delay_us)      # the confined launch gets its CTAs resident before the deposit asks for SMs
+        f, fs = self.pm_mesh(pos)
+        eng.p3m_mesh_done()
+        mk("p3m_short(join)", lambda: main.wait_stream(sr))
+        return f, fs
+
     def pp(self, pos, acc, n_total: int, periodic=False):
         c = self.cfg
         half = 0.5 * c.boxsize
@@ -736,8 +783,11 @@ class DistForceStepper:
                 mark("gather_kick_drift", lambda: self._gather(pos, mom, None, kick, drift))
             else:   # short range into its own buffer, mesh chain, one fused gather + add + kick + drift
                 acc_s = self._acc_buf(pos.shape[0])
-                self.short_range(pos, acc_s, False)
-                f, fs = self.pm_mesh(pos)
+                if self.overlap is True or (self.overlap == "auto" and pos.shape[0] >= self.overlap_min_particles):
+                    f, fs = self._short_and_mesh_side_by_side(pos, acc_s)
+                else:
+                    self.short_range(pos, acc_s, False)
+                    f, fs = self.pm_mesh(pos)
                 lay = self.mesh.lay
                 mark("gather_kick_drift", lambda: self.eng.gather_kick_drift_add(
                     f, fs, c.gridsize, c.cell, pos, mom, acc_s, None, 1.0, kick, drift, c.boxsize, x0=lay.x0,

@@ -79,11 +79,13 @@ def test_sharded_pp(world):
 
 
 @pytest.mark.parametrize("device_exchange", [True, False])
-@pytest.mark.parametrize("method,world", [("pm", 2), ("p3m", 2), ("pm", 4)])
-def test_sharded_step_with_migration(method, world, device_exchange):
+@pytest.mark.parametrize("method,world,overlap", [("pm", 2, False), ("p3m", 2, False), ("p3m", 2, True), ("pm", 4, False)])
+def test_sharded_step_with_migration(method, world, overlap, device_exchange):
     """A large drift moves particles across slab faces: after the step every rank holds exactly
     the particles of its slab and the union equals the oracle's step.  Both exchange implementations: the
-    device kernels (nb_halo_select / nb_migrate_*, one host sync per step) and the eager torch bookkeeping."""
+    device kernels (nb_halo_select / nb_migrate_*, one host sync per step) and the eager torch bookkeeping.
+    overlap: the pair kernel confined to an SM subset on a side stream beside the mesh chain (here two emulated ranks
+    share one GPU, so the confined launch finds the SMs busy and the unconfined second launch has real work)."""
     L, n, N = 500.0, 12, 24
     pos = zeldovich_particles(n, L, seed=21)
     rs = np.random.RandomState(1)
@@ -93,6 +95,7 @@ def test_sharded_step_with_migration(method, world, device_exchange):
     def fn(st, p, i):
         st.device_exchange = device_exchange
         st.halo_cap_floor = 64          # the capacity formula (identical on all ranks) decides, not the floor
+        st.overlap, st.p3m_sms = overlap, 40
         m = st.eng.to_device(mom[i])
         p2, m2 = st.step(p, m, 0.3, 0.7)
         return p2.cpu().numpy(), m2.cpu().numpy()

@@ -97,7 +97,7 @@ def test_p3m_short_range_clustered_and_empty_cells(F):
 def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
     """The SM-partitioned form of the pair kernel (nb_p3m_set_sm_limit: persistent CTAs on the first SMs pull units
     from a counter, an unconfined second launch takes what is left) gives the accelerations of the plain launch
-    (to the order of the float64 atomics) - also when the GPU is busy at launch time and the confined launch loses CTAs to foreign SMs, and when
+    (to the float32 summation order) - also when the GPU is busy at launch time and the confined launch loses CTAs to foreign SMs, and when
     the stop flag is already up (nb_p3m_mesh_done before the launch resets it)."""
     import torch
     from nbody_b200.engine import default_engine
@@ -122,8 +122,9 @@ def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
         torch.cuda.synchronize()
     finally:
         eng.p3m_set_sm_limit(0)
-    # the same pair terms; float64 atomics across tiles land in a different order
-    assert err(conf, plain) <= 1e-6
+    # the same pair terms in another float32 order: the cell sort places the particles of a cell with atomics, so
+    # two sorts of the same set differ in the order within a cell
+    assert err(conf, plain) <= 5e-6
 
 
 def test_p3m_step_overlapped_equals_sequential(F, monkeypatch):
@@ -142,8 +143,8 @@ def test_p3m_step_overlapped_equals_sequential(F, monkeypatch):
         for _ in range(3):
             st.step(p, m, 0.01, 0.01)
         out.append((p.cpu().numpy(), m.cpu().numpy()))
-    assert np.abs(out[0][0] - out[1][0]).max() <= 1e-9 * L
-    assert err(out[1][1], out[0][1]) <= 1e-6
+    assert np.abs(out[0][0] - out[1][0]).max() <= 1e-7 * L
+    assert err(out[1][1], out[0][1]) <= 5e-6
 
 
 @pytest.mark.parametrize("method", ["pm", "p3m", "pp"])

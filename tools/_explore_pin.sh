@@ -1,13 +1,16 @@
 #!/bin/bash
-# scratch driver for one gpurun call: full GPU suite, smoke, default bench lines
+# scratch driver for one gpurun call: N-GPU bench (N from $1), sequential and overlapped
+N=${1:-2}
 mkdir -p gpurun_out
-python -m pytest tests -q -m gpu -x 2>&1 | tail -8
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
-python bench.py > gpurun_out/r2q_bench_p3m.json 2> gpurun_out/r2q_bench_p3m.err; tail -c 600 gpurun_out/r2q_bench_p3m.err
+python -m pytest tests/test_gpu_dist.py tests/test_gpu_force.py -q -m gpu -x 2>&1 | tail -3
+for ov in 0 auto; do
+NB_P3M_OVERLAP=$ov timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r2s_bench_p3m_${N}gpu_ov$ov.json 2> gpurun_out/r2s_bench_p3m_${N}gpu_ov$ov.err
+echo "rc=$?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/r2s_bench_p3m_${N}gpu_ov$ov.err | tail -c 1500
 python - <<PY
 import json
-d=json.loads(open("gpurun_out/r2q_bench_p3m.json").read().strip().splitlines()[-1])
-print("p3m", d["ms_per_step"], d["value"], d["e2e"], d.get("overlap"), d["clocks"], d["gpu_launches"])
-print({k: d.get(k) for k in ("cpu_baseline",)})
+d=json.loads(open("gpurun_out/r2s_bench_p3m_${N}gpu_ov$ov.json").read().strip().splitlines()[-1])
+print("N=$N ov=$ov", d["ms_per_step"], d["value"], d["e2e"]["value"] if d.get("e2e") else None)
+print(d["phase_ms"]); print(d["roofline"]["kernel"][:20], d["roofline"]["ms"], d["roofline"]["frac"])
+print(d["invariants"]["mom_sq_sum"], d["invariants"]["pos_sum"])
 PY
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2q_bench_ref.json 2> gpurun_out/r2q_bench_ref.err; tail -c 300 gpurun_out/r2q_bench_ref.json
+done
