@@ -97,7 +97,7 @@ def test_p3m_short_range_clustered_and_empty_cells(F):
 def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
     """The SM-partitioned form of the pair kernel (nb_p3m_set_sm_limit: persistent CTAs on the first SMs pull units
     from a counter, an unconfined second launch takes what is left) gives the accelerations of the plain launch
-    (to the float32 summation order) - also when the GPU is busy at launch time and the confined launch loses CTAs to foreign SMs, and when
+    bit for bit on the same sorted set - also when the GPU is busy at launch time and the confined launch loses CTAs to foreign SMs, and when
     the stop flag is already up (nb_p3m_mesh_done before the launch resets it)."""
     import torch
     from nbody_b200.engine import default_engine
@@ -107,7 +107,18 @@ def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
     cfg = cfg_for("p3m", n, N, L)
     st = F.ForceStepper(cfg, eng)
     dpos = eng.to_device(pos)
-    plain = st.short_range(dpos, eng.to_device(np.zeros_like(pos)), accumulate=False).cpu().numpy()
+    # one sort for both launches: the sort places the particles of a cell with atomics, so two sorts of the same
+    # set differ in the order within a cell and the float32 sums with them (4e-6 of the rms between two plain runs)
+    sorted4, perm, cell_start = eng.cell_sort(dpos, L, st.ncs, mass=1.0)
+
+    def pairs():
+        out = eng.to_device(np.zeros_like(pos))
+        eng.p3m_short(sorted4, perm, cell_start, L, st.ncs, cfg.r_s, cfg.r_cut, cfg.eps, scale=cfg.G * cfg.mass, out=out,
+                      accumulate=False)
+        torch.cuda.synchronize()
+        return out.cpu().numpy()
+
+    plain = pairs()
     eng.p3m_set_sm_limit(24)
     try:
         eng.p3m_mesh_done()
@@ -118,13 +129,11 @@ def test_p3m_short_range_confined_to_an_sm_subset(F, busy):
                 big = torch.empty(1 << 28, dtype=torch.float32, device=eng.device)
                 for _ in range(4):
                     big.add_(1.0)
-        conf = st.short_range(dpos, eng.to_device(np.zeros_like(pos)), accumulate=False).cpu().numpy()
-        torch.cuda.synchronize()
+        conf = pairs()
     finally:
         eng.p3m_set_sm_limit(0)
-    # the same pair terms in another float32 order: the cell sort places the particles of a cell with atomics, so
-    # two sorts of the same set differ in the order within a cell
-    assert err(conf, plain) <= 5e-6
+    assert np.abs(plain).max() > 0
+    assert np.array_equal(conf, plain)
 
 
 def test_p3m_step_overlapped_equals_sequential(F, monkeypatch):
@@ -143,8 +152,9 @@ def test_p3m_step_overlapped_equals_sequential(F, monkeypatch):
         for _ in range(3):
             st.step(p, m, 0.01, 0.01)
         out.append((p.cpu().numpy(), m.cpu().numpy()))
-    assert np.abs(out[0][0] - out[1][0]).max() <= 1e-7 * L
-    assert err(out[1][1], out[0][1]) <= 5e-6
+    # two independent cell sorts: float32 summation order within a cell differs (see the test above)
+    assert np.abs(out[0][0] - out[1][0]).max() <= 1e-6 * L
+    assert err(out[1][1], out[0][1]) <= 2e-5
 
 
 @pytest.mark.parametrize("method", ["pm", "p3m", "pp"])
