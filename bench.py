@@ -487,7 +487,8 @@ def run_ours(args):
         line["e2e"] = e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work, unit, L, N,
                                   np_total)
     else:
-        line["e2e"] = e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier)
+        line["e2e"] = e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier,
+                                       stepper=stepper, dts=(dt_kick, dt_drift), np_total=np_total)
     if wl == "p3m" and not args.no_secondary and not args.n:
         # BASELINE.json's metric names PM particle-steps/s and PP Ginteractions/s too: short runs of configs 4
         # and 3 after the headline workload, so that they are driver-observed
@@ -723,9 +724,11 @@ def e2e_measure(torch, eng, method, cfg, stepper, pos, mom, one_step, args, work
                     "deposit + overdensity + power_spectrum_bins on pinned host positions, (count,sum) bins back")}
 
 
-def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier):
+def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit, barrier, stepper=None, dts=(0.0, 0.0),
+                     np_total=0):
     """N > 1: every rank stages ITS shard through pinned host memory each step (H2D of pos+mom,
-    the sharded step, D2H of the updated shard); device time, max over ranks."""
+    the sharded step, D2H of the updated shard); device time, max over ranks.  Force steps go through
+    DistForceStepper.step_host (momentum upload on a side stream under the force computation)."""
     steps = max(1, min(args.steps, 3))
     pos0 = state["pos"]
     hpos = torch.empty(pos0.shape, dtype=torch.float64, pin_memory=True)
@@ -744,6 +747,8 @@ def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit
     torch.cuda.synchronize()
 
     def host_step():
+        if method != "pk":
+            return stepper.step_host(hpos, hmom, opos, omom, dts[0], dts[1], n_total=np_total)
         dpos.copy_(hpos, non_blocking=True)
         state["pos"] = dpos
         if method != "pk":
@@ -774,7 +779,9 @@ def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit
     ms = float(t.item())
     return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
             "h2d_bytes_per_step": int(bt[0].item()), "d2h_bytes_per_step": int(bt[1].item()),
-            "api": "nbody_b200.dist.DistForceStepper.step, each rank's shard staged through pinned host memory"}
+            "api": ("nbody_b200.dist.DistPowerSpectrum, each rank's shard staged through pinned host memory" if method == "pk"
+                    else "nbody_b200.dist.DistForceStepper.step_host on each rank's pinned host shard (H2D pos, mom upload "
+                         "under the force computation, D2H of the migrated shard)")}
 
 
 def main():

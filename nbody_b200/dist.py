@@ -764,22 +764,31 @@ class DistForceStepper:
                 self._raise_flags(0, h_over)
         return acc
 
-    def step(self, pos, mom, dt_kick, dt_drift, mark=None, n_total: int = 0, periodic_pp=False):
+    def step(self, pos, mom, dt_kick, dt_drift, mark=None, n_total: int = 0, periodic_pp=False, tail_waits=None):
+        """tail_waits: a stream the momenta are still being written on (step_host's upload); the step waits for it
+        right before the kick, the first use of `mom`."""
         c = self.cfg
         mark = mark or (lambda name, fn: fn())
         self._mark = mark
+
+        def mom_ready():
+            if tail_waits is not None:
+                torch.cuda.current_stream(self.eng.device).wait_stream(tail_waits)
+
         try:
             kick = c.mass * dt_kick
             drift = dt_drift / (c.mass * c.a * c.a)
             if c.method == "pp":
                 acc = self._acc_buf(pos.shape[0])
                 self.pp(pos, acc, n_total or c.npart, periodic_pp)
+                mom_ready()
                 mark("kick_drift", lambda: self.eng.kick_drift(pos, mom, acc, kick, drift, c.boxsize))
                 return pos, mom
             if self.world > 1:
                 pos, mom = self._own(pos, mom)
             if c.method == "pm":
                 self.pm_mesh(pos)
+                mom_ready()
                 mark("gather_kick_drift", lambda: self._gather(pos, mom, None, kick, drift))
             else:   # short range into its own buffer, mesh chain, one fused gather + add + kick + drift
                 acc_s = self._acc_buf(pos.shape[0])
@@ -789,12 +798,47 @@ class DistForceStepper:
                     self.short_range(pos, acc_s, False)
                     f, fs = self.pm_mesh(pos)
                 lay = self.mesh.lay
+                mom_ready()
                 mark("gather_kick_drift", lambda: self.eng.gather_kick_drift_add(
                     f, fs, c.gridsize, c.cell, pos, mom, acc_s, None, 1.0, kick, drift, c.boxsize, x0=lay.x0,
                     nx_own=lay.nxl, n_ghost=lay.n_ghost))
             return mark("migrate", lambda: self.migrate(pos, mom))
         finally:
             self._mark = lambda name, fn: fn()
+
+    def step_host(self, hpos, hmom, out_pos, out_mom, dt_kick, dt_drift, mark=None, n_total: int = 0,
+                  periodic_pp=False):
+        """One step of this rank's shard on HOST buffers (pinned (n,3) float64 CPU tensors; out_pos / out_mom with
+        room for the particles that migrate in).  Like ForceStepper.step_host: positions are uploaded first, the
+        momenta - first needed by the kick - on a side stream under the force computation, the updated shard is
+        copied back behind the migration.  Asynchronous on the current stream; returns the new particle count
+        of the rank (rows of out_pos / out_mom that are valid once the stream is synchronised)."""
+        dev = self.eng.device
+        n = hpos.shape[0]
+        if self.cfg.method == "pp" or self.world == 1:
+            if self._pbuf is None or self._pbuf.shape[0] < n:
+                self._pbuf = torch.empty((n, 3), dtype=torch.float64, device=dev)
+                self._mbuf = torch.empty((n, 3), dtype=torch.float64, device=dev)
+        else:
+            self._own(self._pbuf[:n] if self._pbuf is not None and self._pbuf.shape[0] >= n
+                      else torch.empty((n, 3), dtype=torch.float64, device=dev))       # reserves the capacity
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        pos, mom = self._pbuf[:n], self._mbuf[:n]
+        self._side.wait_stream(main)                      # earlier readers of the momentum buffer are done
+        pos.copy_(hpos, non_blocking=True)
+        with torch.cuda.stream(self._side):
+            mom.copy_(hmom, non_blocking=True)
+        pos2, mom2 = self.step(pos, mom, dt_kick, dt_drift, mark=mark, n_total=n_total, periodic_pp=periodic_pp,
+                               tail_waits=self._side)
+        k = pos2.shape[0]
+        if k > out_pos.shape[0] or k > out_mom.shape[0]:
+            from ._lib import NbodyError
+            raise NbodyError(f"step_host: {k} particles after migration, output buffers hold {out_pos.shape[0]}")
+        out_pos[:k].copy_(pos2, non_blocking=True)
+        out_mom[:k].copy_(mom2, non_blocking=True)
+        return k
 
 
 # ------------------------------------------------------------------------------- P(k)

@@ -120,6 +120,39 @@ def test_sharded_step_with_migration(method, world, overlap, device_exchange):
     assert d.max() <= 1e-5 * cfg.cell
 
 
+@pytest.mark.parametrize("method", ["pm", "p3m", "pp"])
+def test_sharded_step_host_matches_resident_step(method):
+    """DistForceStepper.step_host (pinned host shard in, migrated shard out, momentum upload on a side stream) gives
+    the particles of the resident sharded step."""
+    L, n, N, world = 500.0, 12, 24, 2
+    pos = zeldovich_particles(n, L, seed=22)
+    mom = np.random.RandomState(2).normal(scale=30.0, size=pos.shape)
+    cfg = cfg_for(method, n, N, L, interlace=(True, True), G=1.0, mass=1.5, a=0.5)
+
+    def fn(st, p, i):
+        m = st.eng.to_device(mom[i])
+        hp = torch.from_numpy(pos[i]).pin_memory()
+        hm = torch.from_numpy(mom[i]).pin_memory()
+        cap = len(i) + 512
+        op = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+        om = torch.empty((cap, 3), dtype=torch.float64).pin_memory()
+        k = st.step_host(hp, hm, op, om, 0.3, 0.7, n_total=pos.shape[0])
+        torch.cuda.synchronize()
+        host = (op[:k].numpy().copy(), om[:k].numpy().copy())
+        st2 = type(st)(cfg, st.eng, comm=st.comm)
+        p2, m2 = st2.step(p, m, 0.3, 0.7, n_total=pos.shape[0])
+        return host, (p2.cpu().numpy(), m2.cpu().numpy())
+
+    res, _ = run_ranks(world, cfg, pos, fn)
+    for host, resident in res:
+        assert host[0].shape == resident[0].shape
+        o1 = np.lexsort((host[1][:, 2], host[1][:, 1], host[1][:, 0]))
+        o2 = np.lexsort((resident[1][:, 2], resident[1][:, 1], resident[1][:, 0]))
+        assert np.abs(host[1][o1] - resident[1][o2]).max() <= 2e-5 * np.abs(resident[1]).max()
+        d = np.abs(host[0][o1] - resident[0][o2])
+        assert np.minimum(d, L - d).max() <= 1e-5 * cfg.cell
+
+
 @pytest.mark.parametrize("world", [1, 2, 4])
 def test_sharded_power_spectrum(world):
     from nbody_b200.dist import DistPowerSpectrum, run_threaded
