@@ -1,14 +1,8 @@
 #!/bin/bash
-# scratch driver for one gpurun call: N-GPU bench (N from $1), overlapped (default)
-N=${1:-2}
+# scratch driver for one gpurun call: ncu launch list + one full capture of the confined pair kernel
 mkdir -p gpurun_out
-if [ "$2" = "tests" ]; then python -m pytest tests/test_gpu_nccl.py tests/test_gpu_force.py -q -m gpu -x 2>&1 | tail -3; fi
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r2s_bench_p3m_${N}gpu.json 2> gpurun_out/r2s_bench_p3m_${N}gpu.err
-echo "rc=$?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/r2s_bench_p3m_${N}gpu.err | tail -c 1500
-python - <<PY
-import json
-d=json.loads(open("gpurun_out/r2s_bench_p3m_${N}gpu.json").read().strip().splitlines()[-1])
-print("N=$N", d["ms_per_step"], d["value"], d["e2e"]["value"] if d.get("e2e") else None)
-print(d["phase_ms"]); print(d["roofline"]["kernel"][:20], d["roofline"]["ms"], d["roofline"]["frac"])
-print(d["invariants"]["mom_sq_sum"], d["invariants"]["pos_sum"])
-PY
+python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_plain.json 2> gpurun_out/r2t_plain.err || { tail -5 gpurun_out/r2t_plain.err; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2t_launches_p3m_c5.csv python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_ncu.log 2>&1
+echo "launch list rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:p3m_short_v6 --launch-skip 2 -c 2 -o gpurun_out/r2t_k5_confined python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_ncu2.log 2>&1
+echo "full rc=$?"; ls -la gpurun_out/*.ncu-rep
