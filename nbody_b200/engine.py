@@ -506,6 +506,8 @@ class Engine:
         coef = self._tab_cache[key]
         if cell_hi is None:
             cell_hi = ncs ** 3
+        if int(cell_lo) == int(cell_hi) and not accumulate:
+            out.zero_()          # nb_p3m_short returns before touching `out` when the cell range is empty
         _lib.check(self.lib.nb_p3m_short(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm), int(ncs),
                                          int(cell_lo), int(cell_hi), L / ncs, float(r_cut), float(r_s), float(eps),
                                          coef.ctypes.data_as(C.c_void_p), int(coef.size), float(u_max),
