@@ -272,6 +272,15 @@ int nb_pp_accel_ewald(nb_ctx* ctx, const void* ipos_xyzw, int64_t ni, const void
  * sorted_xyzw.w must be the uniform mass nb_cell_sort writes. */
 int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
                  void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream);
+/* nb_cell_sort without allocations: no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  Same
+ * arguments and outputs as nb_cell_sort (cell_start bit-identical; the order inside a cell is decided by atomics
+ * in both).  The scratch (cell id per particle, per-cell counters) is a static device array of the library, 9.0 MiB
+ * on every GPU that loads it: at most 2^21 = 2 097 152 particles and 2^18 = 262 144 cells (ncs <= 64); larger
+ * sizes are rejected with NB_EINVAL.  Calls no cudaMalloc / cudaFree / allocating library routine.  All calls share
+ * the array: calls that overlap on one GPU (two streams, two contexts) race. */
+int nb_cell_sort_static(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
+                        void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream);
 int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
                  int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
                  double eps, const double* coef_host, int ncoef, double u_max, double scale,

@@ -53,6 +53,7 @@ PROTOTYPES = {
     "nb_pp_near_fix": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_i32, c_f64, c_f64, c_f64, c_f64, c_f64, c_f64, c_f64,
                                c_i32, c_f64, c_vp, c_vp]),
     "nb_cell_sort": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
+    "nb_cell_sort_static": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
                              c_f64, c_f64, c_i32, c_i64, c_vp, c_vp]),
     "nb_p3m_set_ctas_per_sm": (c_i32, [c_vp, c_i32]),

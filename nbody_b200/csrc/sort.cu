@@ -11,6 +11,8 @@
 //                       valid particles (rows whose x is NaN are skipped: unused halo-buffer slots).
 #include <cub/device/device_scan.cuh>
 
+#include <mutex>
+
 #include "common.cuh"
 
 __device__ __forceinline__ int sort_cell_coord(double x, double L, double inv_cs, int ncs, double* rel, double cs) {
@@ -92,6 +94,113 @@ extern "C" int nb_cell_sort(nb_ctx* ctx, const double* pos, int64_t np, double L
     NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(nc + 1), st));
     sort_scatter_kernel<<<nblk, 256, 0, st>>>(pos, np, L, cs, inv_cs, ncs, (float)mass, (const int*)cell_of,
                                              cell_start, (int*)counts, (float4*)sorted_xyzw, perm);
+    NB_LAUNCHED(ctx);
+  }
+  return NB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// nb_cell_sort_static: the same counting sort for callers that must not allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Its scratch — the cell id of every particle and the per-cell counters — lives in a file-scope
+// device array instead of nb_scratch's cudaMalloc'ed slots, and the prefix sum is a kernel of this file instead
+// of cub's (no temporary storage to size).  Every GPU that loads the library holds the array until exit:
+//   NB_SORT_STATIC_MAX_NP ints (cell ids) + NB_SORT_STATIC_MAX_NC + 1 ints (counters) = 9.0 MiB.
+// All calls share the array and it keeps the last call's contents: the counters are cleared at the start of each
+// call; two calls that overlap on the GPU (different streams, or different contexts on one device) race.
+static constexpr int64_t NB_SORT_STATIC_MAX_NP = (int64_t)1 << 21;    // 2 097 152 particles (128^3)
+static constexpr int64_t NB_SORT_STATIC_MAX_NC = (int64_t)1 << 18;    // 262 144 cells (64^3)
+static __device__ __align__(256) int sort_static_scratch[NB_SORT_STATIC_MAX_NP + NB_SORT_STATIC_MAX_NC + 64];
+
+// exclusive prefix sum of n ints by ONE CTA of 1024 threads (n <= 2^18 + 1: at most 257 rounds)
+__global__ void __launch_bounds__(1024) sort_scan_one_cta_kernel(const int* __restrict__ in, int* __restrict__ out, int n) {
+  __shared__ int warp_tot[32];
+  __shared__ int s_base;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  for (int t0 = 0; t0 < n; t0 += 1024) {
+    const int t = t0 + threadIdx.x;
+    const int v = t < n ? in[t] : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    if (w == 0) {
+      int x = warp_tot[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += up;
+      }
+      warp_tot[lane] = x;          // inclusive over the warps
+    }
+    __syncthreads();
+    const int base = s_base + (w ? warp_tot[w - 1] : 0);
+    if (t < n) out[t] = base + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 0) s_base += warp_tot[31];
+    __syncthreads();
+  }
+}
+
+// device address of the array, looked up once per device with that device current (in host code the array's name
+// is only a host-side stand-in for the symbol, not a pointer a kernel can use)
+static int sort_static_address(int device, int** out) {
+  constexpr int MAX_DEV = 64;
+  static int* addr[MAX_DEV] = {};
+  static std::mutex mu;
+  NB_REQUIRE(device >= 0 && device < MAX_DEV, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[device]) {
+    int* p = nullptr;
+    NB_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, sort_static_scratch));
+    NB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned NULL");
+    addr[device] = p;
+  }
+  *out = addr[device];
+  return NB_OK;
+}
+
+extern "C" int nb_cell_sort_static(nb_ctx* ctx, const double* pos, int64_t np, double L, int ncs, double mass,
+                                   void* sorted_xyzw, int32_t* perm, int32_t* cell_start, void* stream) {
+  NB_REQUIRE(ctx && sorted_xyzw && perm && cell_start && (np == 0 || pos), "NULL argument");
+  NB_REQUIRE(np >= 0 && ncs >= 1 && L > 0, "bad arguments");
+  const int64_t nc = (int64_t)ncs * ncs * ncs;
+  if (np > NB_SORT_STATIC_MAX_NP) {
+    nb_set_error("nb_cell_sort_static: %lld particles exceed the static scratch (at most %lld); use nb_cell_sort",
+                 (long long)np, (long long)NB_SORT_STATIC_MAX_NP);
+    return NB_EINVAL;
+  }
+  if (nc > NB_SORT_STATIC_MAX_NC) {
+    nb_set_error("nb_cell_sort_static: %d^3 cells exceed the static scratch (at most %lld cells); use nb_cell_sort",
+                 ncs, (long long)NB_SORT_STATIC_MAX_NC);
+    return NB_EINVAL;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  int* scratch = nullptr;
+  int rc = sort_static_address(ctx->device, &scratch);
+  if (rc) return rc;
+  int* cell_of = scratch;
+  int* counts = scratch + NB_SORT_STATIC_MAX_NP;
+  NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(nc + 1), st));
+  const double cs = L / ncs, inv_cs = (double)ncs / L;
+  const int nblk = nb_grid_for(ctx, np > 0 ? np : 1, 256, 16);
+  if (np > 0) {
+    sort_count_kernel<<<nblk, 256, 0, st>>>(pos, np, L, cs, inv_cs, ncs, cell_of, counts);
+    NB_LAUNCHED(ctx);
+  }
+  sort_scan_one_cta_kernel<<<1, 1024, 0, st>>>(counts, cell_start, (int)(nc + 1));
+  NB_LAUNCHED(ctx);
+  if (np > 0) {
+    NB_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * (size_t)(nc + 1), st));
+    sort_scatter_kernel<<<nblk, 256, 0, st>>>(pos, np, L, cs, inv_cs, ncs, (float)mass, cell_of, cell_start, counts,
+                                             (float4*)sorted_xyzw, perm);
     NB_LAUNCHED(ctx);
   }
   return NB_OK;

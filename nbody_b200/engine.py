@@ -496,6 +496,19 @@ class Engine:
                                          _ptr(perm), _ptr(cell_start), self.stream), "nb_cell_sort")
         return sorted4, perm, cell_start
 
+    def cell_sort_static(self, pos: torch.Tensor, L: float, ncs: int, sorted4: torch.Tensor, perm: torch.Tensor,
+                         cell_start: torch.Tensor, mass: float = 1.0):
+        """nb_cell_sort_static: the cell sort into caller-provided outputs with the library's static device scratch
+        (no allocation anywhere in the call; at most 2^21 particles and 64^3 cells)."""
+        self._check_pos(pos)
+        n = pos.shape[0]
+        if (sorted4.shape != (n, 4) or sorted4.dtype != torch.float32 or perm.shape != (n,) or perm.dtype != torch.int32
+                or cell_start.shape != (ncs ** 3 + 1,) or cell_start.dtype != torch.int32):
+            raise ValueError("cell_sort_static: sorted4 (n,4) float32, perm (n,) int32, cell_start (ncs^3+1,) int32")
+        _lib.check(self.lib.nb_cell_sort_static(self.ctx, _ptr(pos), n, float(L), int(ncs), float(mass), _ptr(sorted4),
+                                                _ptr(perm), _ptr(cell_start), self.stream), "nb_cell_sort_static")
+        return sorted4, perm, cell_start
+
     def p3m_short(self, sorted4, perm, cell_start, L: float, ncs: int, r_s: float, r_cut: float, eps: float,
                   scale: float, out: torch.Tensor, accumulate: bool = False, cell_lo: int = 0,
                   cell_hi: int | None = None, i_limit: int = 0) -> torch.Tensor:
