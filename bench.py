@@ -731,6 +731,10 @@ def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit
     DistForceStepper.step_host (momentum upload on a side stream under the force computation)."""
     steps = max(1, min(args.steps, 3))
     pos0 = state["pos"]
+    binding = None
+    if os.environ.get("NB_BIND_HOST", "1") == "1":
+        from nbody_b200.dist import bind_host_near_device
+        binding = bind_host_near_device(eng.device.index if eng.device.index is not None else 0)
     hpos = torch.empty(pos0.shape, dtype=torch.float64, pin_memory=True)
     hpos.copy_(pos0)
     if method == "pk":
@@ -779,6 +783,7 @@ def e2e_measure_dist(torch, dist, eng, method, state, one_step, args, work, unit
     ms = float(t.item())
     return {"value": work / (ms * 1e-3), "unit": unit, "ms_per_step": ms, "steps": steps,
             "h2d_bytes_per_step": int(bt[0].item()), "d2h_bytes_per_step": int(bt[1].item()),
+            "host_binding_rank0": binding if binding is not None else "none (topology unreadable or already bound)",
             "api": ("nbody_b200.dist.DistPowerSpectrum, each rank's shard staged through pinned host memory" if method == "pk"
                     else "nbody_b200.dist.DistForceStepper.step_host on each rank's pinned host shard (H2D pos, mom upload "
                          "under the force computation, D2H of the migrated shard)")}

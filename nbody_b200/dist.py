@@ -376,6 +376,40 @@ class SlabMesh:
         self.force[:nc, lay.nxl:].copy_(self.fghost[:nc])
 
 
+def bind_host_near_device(device_index: int):
+    """Restrict the calling process to the CPU cores next to GPU `device_index` (sysfs `local_cpulist` of its PCI
+    function), so that pinned host buffers allocated afterwards are placed (first touch) on the NUMA node the GPU
+    hangs off and every rank of a node stages its shard through its own memory controller instead of rank 0's.
+    Returns {"cpus": n, "numa_node": k} or None when the topology cannot be read or the cores are not in the
+    process's cpuset (nothing is changed then)."""
+    try:
+        pr = torch.cuda.get_device_properties(device_index)
+        bus = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bus}"
+        with open(f"{base}/local_cpulist") as fh:
+            txt = fh.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if not use or use == allowed:
+            return None
+        os.sched_setaffinity(0, use)
+        try:
+            with open(f"{base}/numa_node") as fh:
+                node = int(fh.read().strip())
+        except (OSError, ValueError):
+            node = -1
+        return {"cpus": len(use), "numa_node": node}
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        return None
+
+
 # ------------------------------------------------------------------------------- force step
 class DistForceStepper:
     """One kick-drift step on this rank's particles (pos, mom: contiguous (n,3) float64 on the

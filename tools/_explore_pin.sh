@@ -1,8 +1,15 @@
 #!/bin/bash
-# scratch driver for one gpurun call: ncu launch list + one full capture of the confined pair kernel
+# scratch driver for one gpurun call: N-GPU bench with / without host binding
+N=${1:-4}
 mkdir -p gpurun_out
-python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_plain.json 2> gpurun_out/r2t_plain.err || { tail -5 gpurun_out/r2t_plain.err; exit 1; }
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2t_launches_p3m_c5.csv python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_ncu.log 2>&1
-echo "launch list rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:p3m_short_v6 --launch-skip 2 -c 2 -o gpurun_out/r2t_k5_confined python bench.py --steps 2 --warmup 1 --no-cpu --no-secondary > gpurun_out/r2t_ncu2.log 2>&1
-echo "full rc=$?"; ls -la gpurun_out/*.ncu-rep
+nvidia-smi topo -m > gpurun_out/r2v_topo_${N}gpu.txt 2>&1; nproc >> gpurun_out/r2v_topo_${N}gpu.txt; lscpu | grep -i "numa\|socket\|model name" >> gpurun_out/r2v_topo_${N}gpu.txt
+for b in ${2:-1 0}; do
+NB_BIND_HOST=$b timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r2v_bench_p3m_${N}gpu_bind$b.json 2> gpurun_out/r2v_bench_p3m_${N}gpu_bind$b.err
+echo "rc=$?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/r2v_bench_p3m_${N}gpu_bind$b.err | tail -c 800
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/r2v_bench_p3m_${N}gpu_bind$b.json").read().strip().splitlines()[-1])
+print("N=$N bind=$b", round(d["ms_per_step"],2), "e2e ms", round(d["e2e"]["ms_per_step"],2), d["e2e"].get("host_binding_rank0"))
+PY
+done
+cat gpurun_out/r2v_topo_${N}gpu.txt | head -30
