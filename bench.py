@@ -367,7 +367,7 @@ def run_ours(args):
         mark("gather", lambda: eng.gather_kick_drift(f, fs, N, c.cell, pos, None, acc, 1.0, 0.0, 0.0, L))
         srt = mark("cell_sort", lambda: eng.cell_sort(pos, L, stepper.ncs, mass=1.0))
         mark("p3m_short", lambda: eng.p3m_short(srt[0], srt[1], srt[2], L, stepper.ncs, c.r_s, c.r_cut, c.eps,
-                                                scale=c.G * c.mass, out=acc, accumulate=True))
+                                                scale=c.G * c.mass, out=acc, accumulate=True, **stepper._near(pos)))
         return mark("kick_drift", lambda: eng.kick_drift(pos, mom, acc, c.mass * dt_kick,
                                                          dt_drift / (c.mass * c.a ** 2), L))
 

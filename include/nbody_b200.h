@@ -285,6 +285,17 @@ int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start
                  int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
                  double eps, const double* coef_host, int ncoef, double u_max, double scale,
                  int accumulate, int64_t i_limit, double* acc, void* stream);
+/* nb_p3m_short with the close pairs in float64: the tile coordinates of the pair kernel are float32 in a frame of up
+ * to 4 cells, which a pair at a few softening lengths turns into 1e-4..1e-3 of the rms force.  Here the kernel does
+ * not evaluate an in-range pair with 0 < r < r_near but lists it, and a second kernel evaluates the listed pairs
+ * from pos ((np,3) float64, the array nb_cell_sort sorted; box = periodic box side) with erfc/exp in double.
+ * near_count_out (device int32 or NULL): number of near pairs found; beyond the list capacity (2 np entries, at
+ * least 2^20) pairs keep the float32 evaluation.  No reference source (CONCEPT short range, float64 throughout). */
+int nb_p3m_short_exact(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
+                       int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut, double r_s,
+                       double eps, const double* coef_host, int ncoef, double u_max, double scale, int accumulate,
+                       int64_t i_limit, double* acc, const double* pos, int64_t np, double box, double r_near,
+                       int32_t* near_count_out, void* stream);
 /* Resident CTAs per SM of the nb_p3m_short grid (0 = default: many waves of CTAs).  A value
  * below the kernel's natural residency (4) leaves shared memory / registers on every SM for
  * kernels of another stream (the PM chain of the same step runs concurrently). */

@@ -56,6 +56,8 @@ PROTOTYPES = {
     "nb_cell_sort_static": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "nb_p3m_short": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
                              c_f64, c_f64, c_i32, c_i64, c_vp, c_vp]),
+    "nb_p3m_short_exact": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_i32,
+                                   c_f64, c_f64, c_i32, c_i64, c_vp, c_vp, c_i64, c_f64, c_f64, c_vp, c_vp]),
     "nb_p3m_set_ctas_per_sm": (c_i32, [c_vp, c_i32]),
     "nb_p3m_set_sm_limit": (c_i32, [c_vp, c_i32]),
     "nb_delay_us": (c_i32, [c_vp, c_i32, c_vp]),

@@ -63,6 +63,7 @@ enum NbScratchSlot {
   NB_SCR_SORT1,
   NB_SCR_SORT2,
   NB_SCR_SORT3,
+  NB_SCR_NEAR,        // near-pair list of nb_p3m_short_exact
   NB_SCR_FLAGS,       // a few ints that outlive one call (unit counter / stop flag of the overlapped P3M step)
   NB_SCR_NSLOTS
 };

@@ -14,6 +14,8 @@
 // FP32 in the pair loop, float64 accumulation across neighbour cells.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 #define P3M_WARPS 4
@@ -152,11 +154,47 @@ __device__ __forceinline__ void p3m_sts_u16(unsigned saddr, unsigned short v) {
   asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"(v) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------
+// Near-pair list (nb_p3m_short_exact).  Tile coordinates are float32 in a frame of up to 4 cells, so a separation
+// carries a quantum of ~2.4e-7 x 4 r_cut; a pair at r of a few softening lengths turns that into 1e-4..1e-3 of the
+// rms force.  With a list, phase 2 does not evaluate an in-range pair with 0 < r^2 < rn2: it appends
+// (sorted slot of i, sorted slot of j) to a global list and a float64 kernel evaluates those pairs afterwards from
+// the original positions.  The decision is made once, here, so no pair is counted twice or lost.  When the list is
+// full the pair is evaluated in float32 as before (count keeps counting: the caller can read the overflow).
+struct P3mNearList {
+  int2* list;
+  int* count;
+  int cap;
+  float rn2;
+};
+struct P3mNoNear {};   // tag: kernel generation without a list
+
+template <typename SLOT>
+__device__ __noinline__ void p3m_near_push(const P3mNearList& nl, int i_slot, int v0, int v1, bool& n0, bool& n1,
+                                           const SLOT& slot_of) {
+  const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+  const unsigned m0 = __ballot_sync(0xffffffffu, n0), m1 = __ballot_sync(0xffffffffu, n1);
+  int base = 0;
+  if (lane == 0) base = atomicAdd(nl.count, __popc(m0) + __popc(m1));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (n0) {
+    const int t = base + __popc(m0 & lt);
+    if (t < nl.cap) nl.list[t] = make_int2(i_slot, slot_of(v0)); else n0 = false;
+  }
+  if (n1) {
+    const int t = base + __popc(m0) + __popc(m1 & lt);
+    if (t < nl.cap) nl.list[t] = make_int2(i_slot, slot_of(v1)); else n1 = false;
+  }
+}
+
 // one packed evaluation of two queued candidates (tile slots v0, v1; ok = entry is live)
+template <typename SLOT = P3mNoNear>
 __device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const float* __restrict__ ty,
                                            const float* __restrict__ tz, int v0, int v1, bool ok0, bool ok1,
                                            p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi, const P3m3Packed& k,
-                                           p3m_f32x2& FX, p3m_f32x2& FY, p3m_f32x2& FZ) {
+                                           p3m_f32x2& FX, p3m_f32x2& FY, p3m_f32x2& FZ,
+                                           const P3mNearList& nl = P3mNearList{}, int i_slot = 0,
+                                           const SLOT& slot_of = SLOT{}) {
   const p3m_f32x2 dx = p3m_add2(p3m_pack2(tx[v0], tx[v1]), nxi);
   const p3m_f32x2 dy = p3m_add2(p3m_pack2(ty[v0], ty[v1]), nyi);
   const p3m_f32x2 dz = p3m_add2(p3m_pack2(tz[v0], tz[v1]), nzi);
@@ -174,6 +212,14 @@ __device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const f
   const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
   float s0, s1;
   p3m_unpack2(s, s0, s1);
+  if constexpr (!std::is_same<SLOT, P3mNoNear>::value) {
+    float r2a, r2b;
+    p3m_unpack2(r2, r2a, r2b);
+    bool n0 = ok0 && r2a < nl.rn2 && r2a > 0.f, n1 = ok1 && r2b < nl.rn2 && r2b > 0.f;
+    if (__any_sync(0xffffffffu, n0 || n1)) p3m_near_push(nl, i_slot, v0, v1, n0, n1, slot_of);
+    ok0 = ok0 && !n0;
+    ok1 = ok1 && !n1;
+  }
   const p3m_f32x2 sm = p3m_pack2(ok0 ? s0 : 0.f, ok1 ? s1 : 0.f);
   FX = p3m_fma2(sm, dx, FX);
   FY = p3m_fma2(sm, dy, FY);
@@ -182,17 +228,20 @@ __device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const f
 
 // phase 2: evaluate the queued candidates of every lane, four per round as two independent
 // packed chains (the queue has 4 rows of slack beyond QD, so reading ahead is always in range)
+template <typename SLOT = P3mNoNear>
 __device__ __forceinline__ void p3m4_drain(const float* __restrict__ tx, const float* __restrict__ ty,
                                            const float* __restrict__ tz, const unsigned short* __restrict__ qcol,
                                            int cnt, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
-                                           const P3m3Packed& k, double& ax, double& ay, double& az) {
+                                           const P3m3Packed& k, double& ax, double& ay, double& az,
+                                           const P3mNearList& nl = P3mNearList{}, int i_slot = 0,
+                                           const SLOT& slot_of = SLOT{}) {
   const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
   p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull, GX = 0ull, GY = 0ull, GZ = 0ull;
   for (int r = 0; r < rounds; ++r) {
     const int e = 4 * r;
     const int v0 = qcol[e * 32], v1 = qcol[(e + 1) * 32], v2 = qcol[(e + 2) * 32], v3 = qcol[(e + 3) * 32];
-    p3m4_eval2(tx, ty, tz, v0, v1, e < cnt, e + 1 < cnt, nxi, nyi, nzi, k, FX, FY, FZ);
-    p3m4_eval2(tx, ty, tz, v2, v3, e + 2 < cnt, e + 3 < cnt, nxi, nyi, nzi, k, GX, GY, GZ);
+    p3m4_eval2<SLOT>(tx, ty, tz, v0, v1, e < cnt, e + 1 < cnt, nxi, nyi, nzi, k, FX, FY, FZ, nl, i_slot, slot_of);
+    p3m4_eval2<SLOT>(tx, ty, tz, v2, v3, e + 2 < cnt, e + 3 < cnt, nxi, nyi, nzi, k, GX, GY, GZ, nl, i_slot, slot_of);
   }
   float a, b, c, d;
   p3m_unpack2(FX, a, b); p3m_unpack2(GX, c, d); ax += (double)((a + b) + (c + d));
@@ -204,11 +253,13 @@ __device__ __forceinline__ void p3m4_drain(const float* __restrict__ tx, const f
 // runs full and at the end.  One group = 32 slots: every lane takes slots 4s..4s+3 of both
 // 16-slot rows (s = its j-stream) as one LDS.128 per coordinate, i.e. 8 candidates as four
 // independent packed r² chains; the pushes go through a running pointer into the lane's column.
-template <int QD>
+template <int QD, typename SLOT = P3mNoNear>
 __device__ __forceinline__ void p3m4_pass(const float* __restrict__ tx, const float* __restrict__ ty,
                                           const float* __restrict__ tz, unsigned short* __restrict__ qcol,
                                           int npad, int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
-                                          const P3m3Packed& k, double& ax, double& ay, double& az) {
+                                          const P3m3Packed& k, double& ax, double& ay, double& az,
+                                          const P3mNearList& nl = P3mNearList{}, int i_slot = 0,
+                                          const SLOT& slot_of = SLOT{}) {
   // 32-bit shared-memory address of the next free entry of this lane's column (64 B per row)
   const unsigned qbase = (unsigned)__cvta_generic_to_shared(qcol);
   unsigned qa = qbase;
@@ -236,20 +287,21 @@ __device__ __forceinline__ void p3m4_pass(const float* __restrict__ tx, const fl
       if (r2b < k.rc2) { p3m_sts_u16(qa, (unsigned short)(v + 1)); qa += 64; }
     }
     if (__any_sync(0xffffffffu, qa > qfull)) {
-      p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+      p3m4_drain<SLOT>(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az, nl, i_slot, slot_of);
       qa = qbase;
     }
   }
   if (__any_sync(0xffffffffu, qa != qbase))
-    p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+    p3m4_drain<SLOT>(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az, nl, i_slot, slot_of);
 }
 
-template <bool QUEUE, int QD>
+template <bool QUEUE, int QD, bool NEAR = false>
 __global__ void __launch_bounds__(P3M4_WARPS * 32, QD >= 64 ? 4 : 5)
 p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
-                    const int* __restrict__ cell_list, const int* __restrict__ list_count) {
+                    const int* __restrict__ cell_list, const int* __restrict__ list_count,
+                    P3mNearList nl = P3mNearList{}) {
   extern __shared__ __align__(16) unsigned char p3m4_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int li = lane & 7, strm = lane >> 3;
@@ -335,7 +387,18 @@ p3m_short_v4_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
           __syncwarp();   // every lane is done reading the previous chunk
           p3m4_fill(sorted, roff, rjs, offtab, tx, ty, tz, first, nt, lane);
         }
-        if constexpr (QUEUE)
+        if constexpr (QUEUE && NEAR) {
+          // tile slot v of this chunk is candidate first + v of the flattened 27-cell list
+          auto slot_of = [&](int v) {
+            const int g = first + v;
+            int m = 0;
+#pragma unroll
+            for (int sb = 16; sb > 0; sb >>= 1) m = (roff[m + sb] <= g) ? m + sb : m;
+            return rjs[m] + (g - roff[m]);
+          };
+          p3m4_pass<QD, decltype(slot_of)>(tx, ty, tz, qcol, (nt + 31) & ~31, strm, nxi, nyi, nzi, k, ax, ay, az, nl, i,
+                                           slot_of);
+        } else if constexpr (QUEUE)
           p3m4_pass<QD>(tx, ty, tz, qcol, (nt + 31) & ~31, strm, nxi, nyi, nzi, k, ax, ay, az);
 #ifdef NB_AB_KERNELS
         else   // v3's evaluate-all loop on the v4 tile (A/B: NB_P3M_KERNEL=5)
@@ -398,12 +461,14 @@ __device__ __forceinline__ float4 p3m_lds128(unsigned saddr) {
   return v;
 }
 
-template <int QD, int CAPC>
+template <int QD, int CAPC, typename SLOT = P3mNoNear>
 __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const float* __restrict__ ty,
                                           const float* __restrict__ tz, unsigned txs, unsigned cap4_rt,
                                           unsigned short* __restrict__ qcol, unsigned qbase, int vbeg, int vend,
                                           int strm, p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi,
-                                          const P3m3Packed& k, double& ax, double& ay, double& az) {
+                                          const P3m3Packed& k, double& ax, double& ay, double& az,
+                                          const P3mNearList& nl = P3mNearList{}, int i_slot = 0,
+                                          const SLOT& slot_of = SLOT{}) {
   // CAPC > 0: the tile capacity is a compile-time constant, so the y / z planes are immediate offsets of
   // the running x address (the runtime form cost an LDCU + MOV + 2 LEA per group)
   const unsigned cap4 = CAPC > 0 ? 4u * (unsigned)CAPC : cap4_rt;
@@ -438,12 +503,12 @@ __device__ __forceinline__ void p3m6_pass(const float* __restrict__ tx, const fl
       if (r2b < k.rc2) { p3m_sts_u16(qa, (unsigned short)(v + 1)); qa += 64; }
     }
     if (__any_sync(0xffffffffu, qa > qfull)) {
-      p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+      p3m4_drain<SLOT>(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az, nl, i_slot, slot_of);
       qa = qbase;
     }
   }
   if (__any_sync(0xffffffffu, qa != qbase))
-    p3m4_drain(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az);
+    p3m4_drain<SLOT>(tx, ty, tz, qcol, (int)((qa - qbase) >> 6), nxi, nyi, nzi, k, ax, ay, az, nl, i_slot, slot_of);
 }
 
 #ifdef NB_AB_KERNELS
@@ -472,14 +537,14 @@ __host__ __device__ inline size_t p3m6_cta_bytes(int cap, int qd) {
          P3M6_WARPS * sizeof(unsigned short) * (size_t)(qd + 4) * 32;
 }
 
-template <int QD, int CTAS, bool MASK, int CAPC = 0>
+template <int QD, int CTAS, bool MASK, int CAPC = 0, bool NEAR = false>
 __global__ void __launch_bounds__(P3M6_WARPS * 32, CTAS)
 p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ cell_start,
                     const int* __restrict__ perm, int ncs, int64_t cell_lo, int64_t cell_hi, P3mParams prm,
                     double scale, double* __restrict__ acc, int accumulate, int i_limit, int cap,
                     int* __restrict__ overflow_list, int* __restrict__ overflow_count,
                     int* __restrict__ unit_counter = nullptr, int sm_limit = 0,
-                    const int* __restrict__ stop_flag = nullptr) {
+                    const int* __restrict__ stop_flag = nullptr, P3mNearList nl = P3mNearList{}) {
   // SM partition for the overlapped P3M step (nb_p3m_set_sm_limit): CTAs that land on an SM >= sm_limit leave
   // at once, the others pull their work units from an atomic counter — the pair kernel then occupies the first
   // sm_limit SMs completely (6 CTAs fill their shared memory) and the memory-bound mesh chain of the same step,
@@ -642,6 +707,17 @@ p3m_short_v6_kernel(const float4* __restrict__ sorted, const int* __restrict__ c
                   nyi, nzi, k, ax, ay, az);
       else
 #endif
+      if constexpr (NEAR) {
+        // tile slot -> run (largest m with roff[m] <= v; entries past the last slab equal `total`) -> sorted slot
+        auto slot_of = [&](int v) {
+          int m = 0;
+#pragma unroll
+          for (int sb = 32; sb > 0; sb >>= 1) m = (roff[m + sb] <= v) ? m + sb : m;
+          return rjs[m] + (v - roff[m]);
+        };
+        p3m6_pass<QD, CAPC, decltype(slot_of)>(tx, ty, tz, txs, cap4, qcol, qbase, a_w, b_w, strm, nxi, nyi, nzi, k, ax,
+                                               ay, az, nl, i, slot_of);
+      } else
         p3m6_pass<QD, CAPC>(tx, ty, tz, txs, cap4, qcol, qbase, a_w, b_w, strm, nxi, nyi, nzi, k, ax, ay, az);
       ax += __shfl_xor_sync(0xffffffffu, ax, 8);  ay += __shfl_xor_sync(0xffffffffu, ay, 8);
       az += __shfl_xor_sync(0xffffffffu, az, 8);
@@ -674,11 +750,40 @@ extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
   return NB_OK;
 }
 
+// float64 evaluation of the listed near pairs from the original positions (see P3mNearList): for entry (i, j)
+// acc[perm[i]] += scale * w_j * d / (r^2 + eps^2)^(3/2) * (erfc(u) + 2u/sqrt(pi) exp(-u^2)), d = x_j - x_i (nearest
+// image), u = r / (2 r_s) — the pair term of the short-range sum without the float32 tile coordinates.
+__global__ void __launch_bounds__(256)
+p3m_near_kernel(const int2* __restrict__ list, const int* __restrict__ count, int cap,
+                const float4* __restrict__ sorted, const int* __restrict__ perm, const double* __restrict__ pos,
+                double box, double inv_box, double inv_2rs, double eps2, double scale, double* __restrict__ acc) {
+  const int n = min(*count, cap);
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int2 e = list[t];
+    const int64_t i = perm[e.x], j = perm[e.y];
+    double dx = pos[3 * j] - pos[3 * i], dy = pos[3 * j + 1] - pos[3 * i + 1], dz = pos[3 * j + 2] - pos[3 * i + 2];
+    dx -= box * rint(dx * inv_box);
+    dy -= box * rint(dy * inv_box);
+    dz -= box * rint(dz * inv_box);
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    if (!(r2 > 0.0)) continue;
+    const double u = sqrt(r2) * inv_2rs;
+    const double f = erfc(u) + 1.1283791670955126 * u * exp(-u * u);
+    const double rinv = 1.0 / sqrt(r2 + eps2);
+    const double sfac = scale * (double)sorted[e.y].w * rinv * rinv * rinv * f;
+    atomicAdd(&acc[3 * i], sfac * dx);
+    atomicAdd(&acc[3 * i + 1], sfac * dy);
+    atomicAdd(&acc[3 * i + 2], sfac * dz);
+  }
+}
+
 // coef_host: P3M_DEG+1 doubles (monomial coefficients of Q in t, low to high), HOST pointer.
-extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
-                            int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
-                            double r_s, double eps, const double* coef_host, int ncoef, double u_max,
-                            double scale, int accumulate, int64_t i_limit, double* acc, void* stream) {
+// pos != NULL and r_near > 0: near-pair list (nb_p3m_short_exact).
+static int p3m_short_impl(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
+                          int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
+                          double r_s, double eps, const double* coef_host, int ncoef, double u_max,
+                          double scale, int accumulate, int64_t i_limit, double* acc, const double* pos, int64_t np,
+                          double box, double r_near, int32_t* near_count_out, void* stream) {
   NB_REQUIRE(ctx && sorted_xyzw && cell_start && perm && coef_host && acc, "NULL argument");
   NB_REQUIRE(ncoef == P3M_DEG + 1, "split polynomial must have 11 coefficients");
   NB_REQUIRE(ncs >= 3, "need at least 3 cells per side (27 distinct neighbours)");
@@ -686,9 +791,12 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
   NB_REQUIRE(r_cut / (2 * r_s) <= u_max * (1 + 1e-9), "polynomial range does not cover r_cut");
   const int64_t nc = (int64_t)ncs * ncs * ncs;
   NB_REQUIRE(cell_lo >= 0 && cell_hi <= nc && cell_lo <= cell_hi, "bad cell range");
-  if (cell_lo == cell_hi) return NB_OK;
   cudaStream_t st = (cudaStream_t)stream;
   NB_CHECK_CUDA(cudaSetDevice(ctx->device));
+  if (cell_lo == cell_hi) {
+    if (near_count_out) NB_CHECK_CUDA(cudaMemsetAsync(near_count_out, 0, sizeof(int32_t), st));
+    return NB_OK;
+  }
   P3mParams prm;
   prm.rc2 = (float)(r_cut * r_cut);
   prm.eps2 = (float)(eps * eps);
@@ -713,6 +821,22 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
     int* ovf_count = (int*)ovf;
     int* ovf_list = ovf_count + 4;
     NB_CHECK_CUDA(cudaMemsetAsync(ovf_count, 0, sizeof(int), st));
+    // near-pair list: 2 entries per particle (a uniform set has 0.5 partners per particle inside 20 softening
+    // lengths); pairs beyond the capacity stay with the float32 evaluation
+    const bool near = pos != nullptr && r_near > 0.0;
+    P3mNearList nl{};
+    if (near) {
+      const int64_t want = 2 * np > ((int64_t)1 << 20) ? 2 * np : ((int64_t)1 << 20);
+      const int64_t ncap = want < 0x7ffffff0 ? want : 0x7ffffff0;
+      void* nb = nullptr;
+      rc = nb_scratch(ctx, NB_SCR_NEAR, sizeof(int2) * (size_t)ncap + 256, &nb);
+      if (rc) return rc;
+      nl.count = (int*)nb;
+      nl.list = (int2*)((char*)nb + 256);
+      nl.cap = (int)ncap;
+      nl.rn2 = (float)(r_near * r_near);
+      NB_CHECK_CUDA(cudaMemsetAsync(nl.count, 0, sizeof(int), st));
+    }
     const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
     const int64_t nunits = ((cell_hi + ncs - 1) / ncs - cell_lo / ncs) * nrun;
     int64_t nblk = nunits < cap ? nunits : cap;
@@ -725,34 +849,65 @@ extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t*
       NB_CHECK_CUDA(cudaMemsetAsync(unit_counter, 0, 2 * sizeof(int), st));
       nblk = (int64_t)ctx->num_sms * 6;
     }
-    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v6_kernel<QD6, 6, false, CAP6>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem6));
-    p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+    auto k6 = near ? p3m_short_v6_kernel<QD6, 6, false, CAP6, true> : p3m_short_v6_kernel<QD6, 6, false, CAP6, false>;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(k6, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem6));
+    k6<<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
         (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim, CAP6,
-        ovf_list, ovf_count, unit_counter, ctx->p3m_sm_limit, unit_counter ? unit_counter + 1 : nullptr);
+        ovf_list, ovf_count, unit_counter, ctx->p3m_sm_limit, unit_counter ? unit_counter + 1 : nullptr, nl);
     NB_LAUNCHED(ctx);
     if (unit_counter) {
       // second, unconfined launch on the same counter: the units left when the mesh chain raised the stop flag —
       // and every unit, should the confined launch have found the SMs busy and lost its CTAs (a CTA that exits
       // on a foreign SM is not replaced).  Empty when the confined CTAs got through the list.
-      p3m_short_v6_kernel<QD6, 6, false, CAP6><<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
+      k6<<<(int)nblk, P3M6_WARPS * 32, smem6, st>>>(
           (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim,
-          CAP6, ovf_list, ovf_count, unit_counter, 0, nullptr);
+          CAP6, ovf_list, ovf_count, unit_counter, 0, nullptr, nl);
       NB_LAUNCHED(ctx);
     }
     const int tile_cap = P3M4_CAP;
     const size_t smem4 = 96 * sizeof(float) + P3M4_WARPS * p3m4_warp_bytes(tile_cap, 64);
-    NB_CHECK_CUDA(cudaFuncSetAttribute(p3m_short_v4_kernel<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem4));
-    p3m_short_v4_kernel<true, 64><<<ctx->num_sms * 4, P3M4_WARPS * 32, smem4, st>>>(
+    auto k4 = near ? p3m_short_v4_kernel<true, 64, true> : p3m_short_v4_kernel<true, 64, false>;
+    NB_CHECK_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4));
+    k4<<<ctx->num_sms * 4, P3M4_WARPS * 32, smem4, st>>>(
         (const float4*)sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, prm, scale, acc, accumulate, ilim,
-        tile_cap, ovf_list, ovf_count);
+        tile_cap, ovf_list, ovf_count, nl);
+    if (near) {
+      NB_LAUNCHED(ctx);
+      p3m_near_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(nl.list, nl.count, nl.cap, (const float4*)sorted_xyzw, perm, pos,
+                                                        box, 1.0 / box, 1.0 / (2.0 * r_s), eps * eps, scale, acc);
+      if (near_count_out)
+        NB_CHECK_CUDA(cudaMemcpyAsync(near_count_out, nl.count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    }
   }
 #else
+  (void)pos; (void)np; (void)box; (void)r_near; (void)near_count_out;   // A/B builds: no near-pair list
 #include "p3m_ab_dispatch.inc"
 #endif
   NB_LAUNCHED(ctx);
   return NB_OK;
+}
+
+extern "C" int nb_p3m_short(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start, const int32_t* perm,
+                            int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side, double r_cut,
+                            double r_s, double eps, const double* coef_host, int ncoef, double u_max,
+                            double scale, int accumulate, int64_t i_limit, double* acc, void* stream) {
+  return p3m_short_impl(ctx, sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, cell_side, r_cut, r_s, eps, coef_host,
+                        ncoef, u_max, scale, accumulate, i_limit, acc, nullptr, 0, 0.0, 0.0, nullptr, stream);
+}
+
+// nb_p3m_short with the pairs closer than r_near evaluated in float64 from the original positions `pos` ((np,3)
+// float64, the array nb_cell_sort sorted; box = side of the periodic box).  near_count_out (device int32, may be
+// NULL) receives the number of near pairs found; pairs beyond the list capacity (2 np entries, at least 2^20) were
+// evaluated in float32 like nb_p3m_short does.
+extern "C" int nb_p3m_short_exact(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* cell_start,
+                                  const int32_t* perm, int ncs, int64_t cell_lo, int64_t cell_hi, double cell_side,
+                                  double r_cut, double r_s, double eps, const double* coef_host, int ncoef,
+                                  double u_max, double scale, int accumulate, int64_t i_limit, double* acc,
+                                  const double* pos, int64_t np, double box, double r_near, int32_t* near_count_out,
+                                  void* stream) {
+  NB_REQUIRE(pos && np > 0 && box > 0 && r_near > 0 && r_near < r_cut, "bad near-pair arguments");
+  return p3m_short_impl(ctx, sorted_xyzw, cell_start, perm, ncs, cell_lo, cell_hi, cell_side, r_cut, r_s, eps, coef_host,
+                        ncoef, u_max, scale, accumulate, i_limit, acc, pos, np, box, r_near, near_count_out, stream);
 }
 
 // Pair statistics of the same traversal (not timed; bench.py uses it to convert the kernel

@@ -444,6 +444,7 @@ class DistForceStepper:
         self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "0"))
         self.p3m_delay_us = int(os.environ.get("NB_P3M_DELAY_US", "40"))
         self._sr_stream = None
+        self.p3m_near_fix = os.environ.get("NB_P3M_NEAR", "0") == "1"
         if cfg.method in ("pm", "p3m"):
             self.nb = 2 if cfg.interlace[0] else 1
             self.nc = 6 if cfg.interlace[1] else 3
@@ -602,14 +603,17 @@ class DistForceStepper:
         cx_hi = min(self.ncs, int(math.floor((lay.x0 + lay.nxl) * c.cell / cs)) + 2)
         plane = self.ncs * self.ncs
         self.last_sorted = (sorted4, cell_start)
-        return sorted4, perm, cell_start, cx_lo * plane, cx_hi * plane, n
+        return sorted4, perm, cell_start, cx_lo * plane, cx_hi * plane, n, allp
 
     def _short_pairs(self, prep, acc, accumulate):
         c = self.cfg
-        sorted4, perm, cell_start, cell_lo, cell_hi, n = prep
+        sorted4, perm, cell_start, cell_lo, cell_hi, n, allp = prep
+        near = {}
+        if self.p3m_near_fix and c.eps > 0 and 20.0 * c.eps < c.r_cut:      # as ForceStepper._near
+            near = {"pos": allp, "r_near": 20.0 * c.eps}
         return self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut, c.eps,
                                   scale=c.G * c.mass, out=acc, accumulate=accumulate, cell_lo=cell_lo, cell_hi=cell_hi,
-                                  i_limit=n)
+                                  i_limit=n, **near)
 
     def short_range(self, pos, acc, accumulate=True):
         prep = self._short_prepare(pos)
@@ -636,7 +640,7 @@ class DistForceStepper:
                 mk("p3m_short(side stream, confined)", lambda: self._short_pairs(prep, acc_s, False))
         finally:
             eng.p3m_set_sm_limit(0)
-        for t in prep[:3]:
+        for t in prep[:3] + (prep[6],):
             t.record_stream(sr)
         eng.delay_us(self.p3m_delay_us)      # the confined launch gets its CTAs resident before the deposit asks for SMs
         f, fs = self.pm_mesh(pos)

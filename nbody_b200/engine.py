@@ -511,7 +511,10 @@ class Engine:
 
     def p3m_short(self, sorted4, perm, cell_start, L: float, ncs: int, r_s: float, r_cut: float, eps: float,
                   scale: float, out: torch.Tensor, accumulate: bool = False, cell_lo: int = 0,
-                  cell_hi: int | None = None, i_limit: int = 0) -> torch.Tensor:
+                  cell_hi: int | None = None, i_limit: int = 0, pos: torch.Tensor | None = None,
+                  r_near: float = 0.0, near_count: torch.Tensor | None = None) -> torch.Tensor:
+        """pos (the (n,3) float64 array the sort was made from) and r_near > 0: nb_p3m_short_exact — pairs closer than
+        r_near are evaluated in float64 from pos; near_count (int32 device scalar) receives their number."""
         u_max = r_cut / (2 * r_s) * 1.0001
         key = ("split", round(u_max, 9))
         if key not in self._tab_cache:
@@ -521,6 +524,16 @@ class Engine:
             cell_hi = ncs ** 3
         if int(cell_lo) == int(cell_hi) and not accumulate:
             out.zero_()          # nb_p3m_short returns before touching `out` when the cell range is empty
+        if pos is not None and r_near > 0.0:
+            self._check_pos(pos)
+            _lib.check(self.lib.nb_p3m_short_exact(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm), int(ncs),
+                                                   int(cell_lo), int(cell_hi), L / ncs, float(r_cut), float(r_s),
+                                                   float(eps), coef.ctypes.data_as(C.c_void_p), int(coef.size),
+                                                   float(u_max), float(scale), int(bool(accumulate)), int(i_limit),
+                                                   _ptr(out), _ptr(pos), pos.shape[0], float(L), float(r_near),
+                                                   _ptr(near_count) if near_count is not None else C.c_void_p(0),
+                                                   self.stream), "nb_p3m_short_exact")
+            return out
         _lib.check(self.lib.nb_p3m_short(self.ctx, _ptr(sorted4), _ptr(cell_start), _ptr(perm), int(ncs),
                                          int(cell_lo), int(cell_hi), L / ncs, float(r_cut), float(r_s), float(eps),
                                          coef.ctypes.data_as(C.c_void_p), int(coef.size), float(u_max),

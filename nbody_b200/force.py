@@ -30,6 +30,10 @@ class ForceStepper:
         self.eng = engine or default_engine()
         self.pp_variant = pp_variant
         self.pp_near_fix = True
+        # P3M short range with the pairs inside 20 softening lengths in float64 (nb_p3m_short_exact): 99.9 % of the
+        # particles within 1e-6 of the float64 sum instead of 3e-5, for +28 % pair-kernel time - off by
+        # default, NB_P3M_NEAR=1 or this attribute turns it on
+        self.p3m_near_fix = os.environ.get("NB_P3M_NEAR", "0") == "1"
         self._force = None
         self._force_s = None
         self._acc = None
@@ -83,11 +87,20 @@ class ForceStepper:
                                pref=pref, out=f, out_shifted=fs)
         return f, fs
 
+    def _near(self, pos):
+        """Keyword arguments of engine.p3m_short for the float64 near-pair pass (pairs inside 20 softening lengths,
+        as for PP), or nothing when it is switched off / there is no softening scale."""
+        c = self.cfg
+        r_near = 20.0 * c.eps
+        if not self.p3m_near_fix or c.eps <= 0 or r_near >= c.r_cut:
+            return {}
+        return {"pos": pos, "r_near": r_near}
+
     def short_range(self, pos, acc, accumulate=True):
         c = self.cfg
         sorted4, perm, cell_start = self.eng.cell_sort(pos, c.boxsize, self.ncs, mass=1.0)
         self.eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut, c.eps,
-                           scale=c.G * c.mass, out=acc, accumulate=accumulate)
+                           scale=c.G * c.mass, out=acc, accumulate=accumulate, **self._near(pos))
         return acc
 
     def pp(self, pos, acc, periodic=False):
@@ -159,7 +172,7 @@ class ForceStepper:
                     sorted_ev = torch.cuda.Event()
                     sorted_ev.record(sr_stream)
                     eng.p3m_short(sorted4, perm, cell_start, c.boxsize, self.ncs, c.r_s, c.r_cut, c.eps,
-                                  scale=c.G * c.mass, out=self._acc_s, accumulate=False)
+                                  scale=c.G * c.mass, out=self._acc_s, accumulate=False, **self._near(pos))
                 pm_stream.wait_event(sorted_ev)
                 with torch.cuda.stream(pm_stream):
                     eng.delay_us(self.p3m_delay_us)
