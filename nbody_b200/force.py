@@ -122,7 +122,7 @@ class ForceStepper:
                                  scale=c.G * c.mass, mass=1.0)
         return acc
 
-    def _tail_to_host(self, tail, pos, mom, out_pos, out_mom, chunks=8):
+    def _tail_to_host(self, tail, pos, mom, out_pos, out_mom, chunks=8, join=True):
         """Run the per-particle tail kernel `tail(a, b)` chunk by chunk and copy each finished chunk of
         pos/mom to the host buffers on a side stream, so that the device->host copies (the longest part
         of step_host at the C5 size) start as soon as the first chunk is done."""
@@ -142,9 +142,10 @@ class ForceStepper:
             with torch.cuda.stream(cs):
                 out_pos[a:b].copy_(pos[a:b], non_blocking=True)
                 out_mom[a:b].copy_(mom[a:b], non_blocking=True)
-        main.wait_stream(cs)
+        if join:
+            main.wait_stream(cs)
 
-    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None):
+    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None, join=True):
         """Cell sort + pair kernel into a separate buffer, mesh chain, then ONE fused kernel:
         g = gather(mesh) + short; acc_out <- g and/or kick + drift.  With self.overlap the two
         parts run on two streams and two disjoint sets of SMs."""
@@ -193,7 +194,7 @@ class ForceStepper:
             self._tail_to_host(lambda a, b: eng.gather_kick_drift_add(f, fs, c.gridsize, c.cell, pos[a:b], mom[a:b],
                                                                       self._acc_s[a:b], None, 1.0, kick, drift,
                                                                       c.boxsize),
-                               pos, mom, host_out[0], host_out[1])
+                               pos, mom, host_out[0], host_out[1], join=join)
             return
         eng.gather_kick_drift_add(f, fs, c.gridsize, c.cell, pos, mom, self._acc_s, acc_out, 1.0, kick, drift,
                                   c.boxsize)
@@ -268,6 +269,61 @@ class ForceStepper:
         self.eng.kick_drift(pos, mom, acc, kick, drift, c.boxsize)
         return pos, mom
 
+
+    def step_host_pipelined(self, hpos: torch.Tensor, hmom: torch.Tensor, out_pos: torch.Tensor, out_mom: torch.Tensor,
+                            dt_kick: float, dt_drift: float):
+        """step_host for a stream of INDEPENDENT particle sets (PM / P3M): two sets of device buffers, so the upload of
+        call k+1 runs while call k computes and downloads (PCIe is full duplex and the copy engines run beside the
+        kernels).  Every call still uploads its own positions and momenta and downloads its own result; calls return
+        at once, and `finish_host()` makes the current stream wait for the downloads in flight - call it (and
+        synchronise) before reading out_pos / out_mom or reusing hpos / hmom.  The steps of ONE time loop depend on
+        each other and keep their particles on the device: this is for batches (many snapshots, many runs)."""
+        c, eng = self.cfg, self.eng
+        if c.method not in ("pm", "p3m"):
+            raise ValueError("step_host_pipelined: PM / P3M only")
+        n = hpos.shape[0]
+        dev = eng.device
+        if getattr(self, "_pipe", None) is None or self._pipe["n"] != n:
+            self._pipe = {"n": n, "k": 0, "up": torch.cuda.Stream(device=dev),
+                          "sets": [(torch.empty((n, 3), dtype=torch.float64, device=dev),
+                                    torch.empty((n, 3), dtype=torch.float64, device=dev)) for _ in range(2)],
+                          "free": [None, None]}
+            if getattr(self, "_copy_stream", None) is None:
+                self._copy_stream = torch.cuda.Stream(device=dev)
+        pp = self._pipe
+        b = pp["k"] & 1
+        pp["k"] += 1
+        dpos, dmom = pp["sets"][b]
+        up, main = pp["up"], torch.cuda.current_stream(dev)
+        if pp["free"][b] is not None:
+            up.wait_event(pp["free"][b])                  # the download of the call that used this set is done
+        else:
+            up.wait_stream(main)
+        with torch.cuda.stream(up):
+            dpos.copy_(hpos, non_blocking=True)
+            pos_ev = torch.cuda.Event()
+            pos_ev.record(up)
+            dmom.copy_(hmom, non_blocking=True)
+        main.wait_event(pos_ev)
+        kick = c.mass * dt_kick
+        drift = dt_drift / (c.mass * c.a * c.a)
+        if c.method == "pm":
+            f, fs = self.pm_mesh(dpos)
+            main.wait_stream(up)
+            self._tail_to_host(lambda a, e: eng.gather_kick_drift(f, fs, c.gridsize, c.cell, dpos[a:e], dmom[a:e], None,
+                                                                  1.0, kick, drift, c.boxsize),
+                               dpos, dmom, out_pos, out_mom, join=False)
+        else:
+            self._p3m_fused(dpos, dmom, None, kick, drift, tail_waits=up, host_out=(out_pos, out_mom), join=False)
+        ev = torch.cuda.Event()
+        ev.record(self._copy_stream)
+        pp["free"][b] = ev
+        return out_pos, out_mom
+
+    def finish_host(self):
+        """Current stream waits for the downloads of step_host_pipelined calls in flight."""
+        if getattr(self, "_copy_stream", None) is not None:
+            torch.cuda.current_stream(self.eng.device).wait_stream(self._copy_stream)
 
     def step_host(self, hpos: torch.Tensor, hmom: torch.Tensor, out_pos: torch.Tensor, out_mom: torch.Tensor,
                   dt_kick: float, dt_drift: float, periodic_pp: bool = False):
