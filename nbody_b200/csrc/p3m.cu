@@ -166,6 +166,8 @@ struct P3mNearList {
   int* count;
   int cap;
   float rn2;
+  float rb2;    // pairs with r^2 >= rb2 (the last float32 quanta below the widened cut-off) are listed too: the float64
+                // kernel applies the cut-off to them, so a pair is inside r_cut for both partners or for neither
 };
 struct P3mNoNear {};   // tag: kernel generation without a list
 
@@ -215,7 +217,8 @@ __device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const f
   if constexpr (!std::is_same<SLOT, P3mNoNear>::value) {
     float r2a, r2b;
     p3m_unpack2(r2, r2a, r2b);
-    bool n0 = ok0 && r2a < nl.rn2 && r2a > 0.f, n1 = ok1 && r2b < nl.rn2 && r2b > 0.f;
+    bool n0 = ok0 && (r2a < nl.rn2 || r2a >= nl.rb2) && r2a > 0.f;
+    bool n1 = ok1 && (r2b < nl.rn2 || r2b >= nl.rb2) && r2b > 0.f;
     if (__any_sync(0xffffffffu, n0 || n1)) p3m_near_push(nl, i_slot, v0, v1, n0, n1, slot_of);
     ok0 = ok0 && !n0;
     ok1 = ok1 && !n1;
@@ -756,7 +759,8 @@ extern "C" int nb_p3m_set_ctas_per_sm(nb_ctx* ctx, int ctas_per_sm) {
 __global__ void __launch_bounds__(256)
 p3m_near_kernel(const int2* __restrict__ list, const int* __restrict__ count, int cap,
                 const float4* __restrict__ sorted, const int* __restrict__ perm, const double* __restrict__ pos,
-                double box, double inv_box, double inv_2rs, double eps2, double scale, double* __restrict__ acc) {
+                double box, double inv_box, double inv_2rs, double eps2, double rc2, double scale,
+                double* __restrict__ acc) {
   const int n = min(*count, cap);
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
     const int2 e = list[t];
@@ -766,7 +770,7 @@ p3m_near_kernel(const int2* __restrict__ list, const int* __restrict__ count, in
     dy -= box * rint(dy * inv_box);
     dz -= box * rint(dz * inv_box);
     const double r2 = dx * dx + dy * dy + dz * dz;
-    if (!(r2 > 0.0)) continue;
+    if (!(r2 > 0.0) || r2 >= rc2) continue;      // the cut-off, decided in float64 for the pairs of the boundary shell
     const double u = sqrt(r2) * inv_2rs;
     const double f = erfc(u) + 1.1283791670955126 * u * exp(-u * u);
     const double rinv = 1.0 / sqrt(r2 + eps2);
@@ -835,6 +839,10 @@ static int p3m_short_impl(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* c
       nl.list = (int2*)((char*)nb + 256);
       nl.cap = (int)ncap;
       nl.rn2 = (float)(r_near * r_near);
+      // boundary shell: the float32 range test runs against r_cut^2 (1 + 8e-6) and everything from r_cut^2 (1 - 8e-6)
+      // up goes to the list (tile coordinates carry 2^-21 of 4 cell sides: 2e-6 of r_cut^2 in a squared separation)
+      nl.rb2 = (float)(r_cut * r_cut * (1.0 - 8e-6));
+      prm.rc2 = (float)(r_cut * r_cut * (1.0 + 8e-6));
       NB_CHECK_CUDA(cudaMemsetAsync(nl.count, 0, sizeof(int), st));
     }
     const int nrun = (ncs + P3M6_WARPS - 1) / P3M6_WARPS;
@@ -874,7 +882,8 @@ static int p3m_short_impl(nb_ctx* ctx, const void* sorted_xyzw, const int32_t* c
     if (near) {
       NB_LAUNCHED(ctx);
       p3m_near_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(nl.list, nl.count, nl.cap, (const float4*)sorted_xyzw, perm, pos,
-                                                        box, 1.0 / box, 1.0 / (2.0 * r_s), eps * eps, scale, acc);
+                                                        box, 1.0 / box, 1.0 / (2.0 * r_s), eps * eps, r_cut * r_cut,
+                                                        scale, acc);
       if (near_count_out)
         NB_CHECK_CUDA(cudaMemcpyAsync(near_count_out, nl.count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
     }

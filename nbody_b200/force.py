@@ -34,6 +34,7 @@ class ForceStepper:
         # particles within 1e-6 of the float64 sum instead of 3e-5, for +28 % pair-kernel time - off by
         # default, NB_P3M_NEAR=1 or this attribute turns it on
         self.p3m_near_fix = os.environ.get("NB_P3M_NEAR", "0") == "1"
+        self.p3m_near_eps = float(os.environ.get("NB_P3M_RNEAR", "20"))     # r_near in softening lengths
         self._force = None
         self._force_s = None
         self._acc = None
@@ -91,7 +92,7 @@ class ForceStepper:
         """Keyword arguments of engine.p3m_short for the float64 near-pair pass (pairs inside 20 softening lengths,
         as for PP), or nothing when it is switched off / there is no softening scale."""
         c = self.cfg
-        r_near = 20.0 * c.eps
+        r_near = self.p3m_near_eps * c.eps
         if not self.p3m_near_fix or c.eps <= 0 or r_near >= c.r_cut:
             return {}
         return {"pos": pos, "r_near": r_near}

@@ -145,12 +145,12 @@ def test_p3m_128_256_full_against_the_c_oracle():
 
 
 def test_p3m_128_exact_short_range_mode():
-    """The same set with ForceStepper.p3m_near_fix (nb_p3m_short_exact: in-range pairs closer than 20 softening
-    lengths are listed by the pair kernel and evaluated in float64 from the original positions).  Measured: median
-    2.8e-7, 99 % 7.3e-7, 99.9 % 9.8e-7 of the rms force.  What is left in the max norm (1.6e-4, a handful of
-    particles, none of them with a close partner) is the cut-off itself: a pair within a float32 quantum of r_cut
-    is counted by one side and not by the other, and its whole term - 1.5e-3 of a bare pair force at 4.5 r_s - is
-    the difference."""
+    """The same set with ForceStepper.p3m_near_fix (nb_p3m_short_exact): the pair kernel lists the in-range pairs
+    closer than 20 softening lengths AND the pairs within 8e-6 (relative, in r^2) of the cut-off instead of evaluating
+    them, and a float64 kernel evaluates the list from the original positions (applying the cut-off itself for the
+    boundary shell, so a pair is inside r_cut for both partners or for neither).  north_star's 1e-5 then holds in the
+    MAX norm over all 2.1 M particles: measured median 2.8e-7, 99.9 % 9.6e-7, max 2.5e-6 of the rms force (r_near =
+    12 eps: max 5.9e-6; 8 eps: 1.3e-5)."""
     import torch
     from nbody_b200 import force as F
     from nbody_b200.engine import default_engine
@@ -167,8 +167,7 @@ def test_p3m_128_exact_short_range_mode():
     acc = st.accel(dpos).cpu().numpy()
     ref = cpu_step.accel(cfg, pos)
     e, far = _per_particle_stats(acc, ref, pos, L, cfg.eps, "P3M 128^3/256^3 full, near pairs in float64")
-    assert np.median(e) <= 1e-6 and np.percentile(e, 99.9) <= TOL and e.max() <= 5e-4
-    assert (e > TOL).sum() <= 50
+    assert np.median(e) <= 1e-6 and e.max() <= TOL
     # the list is in use: about half a partner per particle inside 20 eps
     srt = eng.cell_sort(dpos, L, st.ncs)
     cnt = torch.zeros(1, dtype=torch.int32, device=eng.device)
