@@ -659,6 +659,20 @@ def rooflines(eng, method, cfg, pos, phase_ms, n, N, L, hbm_peak, peak_src, fp32
               "peak_source": "measured FMA microkernel (max of FFMA / FFMA2, see fp32_peak)"}
         if k5_note:
             fp["ms_note"] = k5_note
+        if world == 1 and cfg.eps > 0 and 20.0 * cfg.eps < cfg.r_cut:
+            # the same launch in the exact mode (pairs inside 20 eps and the cut-off shell in float64; off by default)
+            acc_ = stepper._acc_buf(pos.shape[0])
+            cnt_ = torch.zeros(1, dtype=torch.int32, device=eng.device)
+            tms = []
+            for it in range(3):
+                a_ = torch.cuda.Event(enable_timing=True); b_ = torch.cuda.Event(enable_timing=True)
+                a_.record()
+                eng.p3m_short(srt[0], srt[1], srt[2], L, stepper.ncs, cfg.r_s, cfg.r_cut, cfg.eps, scale=cfg.G * cfg.mass,
+                              out=acc_, accumulate=False, pos=pos, r_near=20.0 * cfg.eps, near_count=cnt_)
+                b_.record(); b_.synchronize()
+                tms.append(a_.elapsed_time(b_))
+            fp["exact_mode"] = {"ms": sum(tms[1:]) / 2, "near_pairs_listed": int(cnt_.item()),
+                                "note": "nb_p3m_short_exact (NB_P3M_NEAR=1): 1e-5 in the max norm, not the timed default"}
     allk = hbm + ([fp] if fp else [])
     # DRAM traffic per launch from the committed ncu --set full captures (profiles/ncu_traffic.json);
     # it cannot be measured live, so it is only filled in for the exact size that was captured
