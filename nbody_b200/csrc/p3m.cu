@@ -171,21 +171,64 @@ struct P3mNearList {
 };
 struct P3mNoNear {};   // tag: kernel generation without a list
 
+// the packed pair term of two candidates: s = w_j (r^2 + eps^2)^(-3/2) (erfc(u) + 2u/sqrt(pi) exp(-u^2)) and the
+// separations it multiplies
+__device__ __forceinline__ void p3m4_term2(const float* __restrict__ tx, const float* __restrict__ ty,
+                                           const float* __restrict__ tz, int v0, int v1, p3m_f32x2 nxi, p3m_f32x2 nyi,
+                                           p3m_f32x2 nzi, const P3m3Packed& k, p3m_f32x2& s, p3m_f32x2& dx,
+                                           p3m_f32x2& dy, p3m_f32x2& dz, p3m_f32x2& r2) {
+  dx = p3m_add2(p3m_pack2(tx[v0], tx[v1]), nxi);
+  dy = p3m_add2(p3m_pack2(ty[v0], ty[v1]), nyi);
+  dz = p3m_add2(p3m_pack2(tz[v0], tz[v1]), nzi);
+  r2 = p3m_mul2(dx, dx);
+  r2 = p3m_fma2(dy, dy, r2);
+  r2 = p3m_fma2(dz, dz, r2);
+  const p3m_f32x2 rinv = p3m_rsqrt2(p3m_add2(r2, k.eps2));
+  const p3m_f32x2 w = p3m_mul2(r2, k.ws);                          // u²
+  const p3m_f32x2 u = p3m_mul2(w, p3m_rsqrt2(p3m_add2(w, k.tiny)));
+  const p3m_f32x2 tt = p3m_fma2(w, k.ts, k.m1);
+  p3m_f32x2 q = k.nq[P3M_DEG];
+#pragma unroll
+  for (int d = P3M_DEG - 1; d >= 0; --d) q = p3m_fma2(q, tt, k.nq[d]);
+  const p3m_f32x2 f = p3m_fma2(p3m_mul2(w, u), q, k.one);
+  s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
+}
+
+// Rare path of the near-pair drain: bit b of nm = queue entry e_base + b of this lane was left out of the float32
+// sum.  One entry per lane and trip goes to the list (warp-aggregated append); the self pair (zero term) is
+// dropped; with a full list the pair is evaluated in float32 after all, like the plain kernel does.
 template <typename SLOT>
-__device__ __noinline__ void p3m_near_push(const P3mNearList& nl, int i_slot, int v0, int v1, bool& n0, bool& n1,
-                                           const SLOT& slot_of) {
+__device__ __noinline__ void p3m_near_flush(const P3mNearList& nl, int i_slot, unsigned nm, int e_base,
+                                            const unsigned short* __restrict__ qcol, const float* __restrict__ tx,
+                                            const float* __restrict__ ty, const float* __restrict__ tz,
+                                            p3m_f32x2 nxi, p3m_f32x2 nyi, p3m_f32x2 nzi, const P3m3Packed& k,
+                                            double& ax, double& ay, double& az, const SLOT& slot_of) {
   const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-  const unsigned m0 = __ballot_sync(0xffffffffu, n0), m1 = __ballot_sync(0xffffffffu, n1);
-  int base = 0;
-  if (lane == 0) base = atomicAdd(nl.count, __popc(m0) + __popc(m1));
-  base = __shfl_sync(0xffffffffu, base, 0);
-  if (n0) {
-    const int t = base + __popc(m0 & lt);
-    if (t < nl.cap) nl.list[t] = make_int2(i_slot, slot_of(v0)); else n0 = false;
-  }
-  if (n1) {
-    const int t = base + __popc(m0) + __popc(m1 & lt);
-    if (t < nl.cap) nl.list[t] = make_int2(i_slot, slot_of(v1)); else n1 = false;
+  while (__any_sync(0xffffffffu, nm != 0u)) {
+    const bool have = nm != 0u;
+    const int b = have ? __ffs((int)nm) - 1 : 0;
+    nm &= nm - 1u;                                   // clears the lowest set bit; 0 stays 0
+    const int v = qcol[(e_base + b) * 32];
+    const int j = slot_of(v);
+    const bool want = have && j != i_slot;
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(nl.count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (want) {
+      const int t = base + __popc(m & lt);
+      if (t < nl.cap) {
+        nl.list[t] = make_int2(i_slot, j);
+      } else {
+        p3m_f32x2 s2, dx, dy, dz, r2;
+        p3m4_term2(tx, ty, tz, v, v, nxi, nyi, nzi, k, s2, dx, dy, dz, r2);
+        float s0, s1, d0, d1;
+        p3m_unpack2(s2, s0, s1);
+        p3m_unpack2(dx, d0, d1); ax += (double)(s0 * d0);
+        p3m_unpack2(dy, d0, d1); ay += (double)(s0 * d0);
+        p3m_unpack2(dz, d0, d1); az += (double)(s0 * d0);
+      }
+    }
   }
 }
 
@@ -214,15 +257,6 @@ __device__ __forceinline__ void p3m4_eval2(const float* __restrict__ tx, const f
   const p3m_f32x2 s = p3m_mul2(p3m_mul2(p3m_mul2(rinv, rinv), p3m_mul2(rinv, k.wj)), f);
   float s0, s1;
   p3m_unpack2(s, s0, s1);
-  if constexpr (!std::is_same<SLOT, P3mNoNear>::value) {
-    float r2a, r2b;
-    p3m_unpack2(r2, r2a, r2b);
-    bool n0 = ok0 && (r2a < nl.rn2 || r2a >= nl.rb2) && r2a > 0.f;
-    bool n1 = ok1 && (r2b < nl.rn2 || r2b >= nl.rb2) && r2b > 0.f;
-    if (__any_sync(0xffffffffu, n0 || n1)) p3m_near_push(nl, i_slot, v0, v1, n0, n1, slot_of);
-    ok0 = ok0 && !n0;
-    ok1 = ok1 && !n1;
-  }
   const p3m_f32x2 sm = p3m_pack2(ok0 ? s0 : 0.f, ok1 ? s1 : 0.f);
   FX = p3m_fma2(sm, dx, FX);
   FY = p3m_fma2(sm, dy, FY);
@@ -240,6 +274,48 @@ __device__ __forceinline__ void p3m4_drain(const float* __restrict__ tx, const f
                                            const SLOT& slot_of = SLOT{}) {
   const int rounds = (__reduce_max_sync(0xffffffffu, cnt) + 3) >> 2;
   p3m_f32x2 FX = 0ull, FY = 0ull, FZ = 0ull, GX = 0ull, GY = 0ull, GZ = 0ull;
+  if constexpr (!std::is_same<SLOT, P3mNoNear>::value) {
+    // Near-pair list: four rounds (16 entries per lane) per trip, branch-free like the plain drain so that ptxas
+    // schedules the eight packed chains together; an entry that stays out of the float32 sum (closer than r_near, in
+    // the cut-off shell, or the self pair) sets a bit of nm, and ONE vote per trip sends the warp to the rare path.
+    // Non-negative floats order like their bit patterns: rn2 <= r^2 < rb2 is one unsigned compare of r^2 - rn2.
+    const unsigned lo = __float_as_uint(nl.rn2), span = __float_as_uint(nl.rb2) - lo;
+    auto round = [&](int rr, int q, unsigned& nm) {
+      const int e = 4 * rr;
+      const int v0 = qcol[e * 32], v1 = qcol[(e + 1) * 32], v2 = qcol[(e + 2) * 32], v3 = qcol[(e + 3) * 32];
+      p3m_f32x2 sa, sb, dxa, dya, dza, dxb, dyb, dzb, r2a, r2b;
+      p3m4_term2(tx, ty, tz, v0, v1, nxi, nyi, nzi, k, sa, dxa, dya, dza, r2a);
+      p3m4_term2(tx, ty, tz, v2, v3, nxi, nyi, nzi, k, sb, dxb, dyb, dzb, r2b);
+      float q0, q1, q2, q3, s0, s1, s2, s3;
+      p3m_unpack2(r2a, q0, q1); p3m_unpack2(r2b, q2, q3);
+      p3m_unpack2(sa, s0, s1); p3m_unpack2(sb, s2, s3);
+      const bool ok0 = e < cnt, ok1 = e + 1 < cnt, ok2 = e + 2 < cnt, ok3 = e + 3 < cnt;
+      const bool f0 = ok0 && (__float_as_uint(q0) - lo) < span, f1 = ok1 && (__float_as_uint(q1) - lo) < span;
+      const bool f2 = ok2 && (__float_as_uint(q2) - lo) < span, f3 = ok3 && (__float_as_uint(q3) - lo) < span;
+      if (ok0 && !f0) nm |= 1u << (4 * q);
+      if (ok1 && !f1) nm |= 2u << (4 * q);
+      if (ok2 && !f2) nm |= 4u << (4 * q);
+      if (ok3 && !f3) nm |= 8u << (4 * q);
+      const p3m_f32x2 ma = p3m_pack2(f0 ? s0 : 0.f, f1 ? s1 : 0.f);
+      const p3m_f32x2 mb = p3m_pack2(f2 ? s2 : 0.f, f3 ? s3 : 0.f);
+      FX = p3m_fma2(ma, dxa, FX); FY = p3m_fma2(ma, dya, FY); FZ = p3m_fma2(ma, dza, FZ);
+      GX = p3m_fma2(mb, dxb, GX); GY = p3m_fma2(mb, dyb, GY); GZ = p3m_fma2(mb, dzb, GZ);
+    };
+    int r = 0;
+    for (; r + 4 <= rounds; r += 4) {
+      unsigned nm = 0u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) round(r + q, q, nm);
+      if (__any_sync(0xffffffffu, nm != 0u))
+        p3m_near_flush(nl, i_slot, nm, 4 * r, qcol, tx, ty, tz, nxi, nyi, nzi, k, ax, ay, az, slot_of);
+    }
+    for (; r < rounds; ++r) {
+      unsigned nm = 0u;
+      round(r, 0, nm);
+      if (__any_sync(0xffffffffu, nm != 0u))
+        p3m_near_flush(nl, i_slot, nm, 4 * r, qcol, tx, ty, tz, nxi, nyi, nzi, k, ax, ay, az, slot_of);
+    }
+  } else
   for (int r = 0; r < rounds; ++r) {
     const int e = 4 * r;
     const int v0 = qcol[e * 32], v1 = qcol[(e + 1) * 32], v2 = qcol[(e + 2) * 32], v3 = qcol[(e + 3) * 32];

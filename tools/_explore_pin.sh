@@ -1,12 +1,10 @@
 #!/bin/bash
-# scratch driver for one gpurun call: N-GPU default bench (N from $1)
-N=${1:-8}
 mkdir -p gpurun_out
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/r2final_bench_p3m_${N}gpu.json 2> gpurun_out/r2final_bench_p3m_${N}gpu.err
-echo "rc=$?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/r2final_bench_p3m_${N}gpu.err | tail -c 1000
+python -m pytest tests/test_gpu_baseline_sizes.py -q -m gpu -x -s -k "exact" 2>&1 | grep -i "P3M 128\|near pairs\|passed\|failed\|rror" | head -4
+NB_P3M_NEAR=1 python -m pytest tests/test_gpu_force.py tests/test_gpu_dist.py tests/test_gpu_force_large.py -q -m gpu -x 2>&1 | tail -2
+NB_P3M_NEAR=1 python bench.py --steps 5 --warmup 3 --no-secondary --no-cpu > gpurun_out/r3a_bench_near1.json 2> gpurun_out/r3a.err || tail -3 gpurun_out/r3a.err
 python - <<PY
 import json
-d=json.loads(open("gpurun_out/r2final_bench_p3m_${N}gpu.json").read().strip().splitlines()[-1])
-print("N=$N", round(d["ms_per_step"],2), d["value"], round(d["e2e"]["ms_per_step"],1), d["clocks"])
-print(d["phase_ms"]); print(d["invariants"]["n_particles_total"], d["invariants"]["mom_sq_sum"])
+d=json.loads(open("gpurun_out/r3a_bench_near1.json").read().strip().splitlines()[-1])
+print("near 1:", round(d["ms_per_step"],2), round(d["phase_ms"]["p3m_short"],2), d["roofline"].get("exact_mode"))
 PY
