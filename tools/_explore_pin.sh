@@ -1,10 +1,10 @@
 #!/bin/bash
+# scratch driver for one gpurun call (development only): full GPU suite, smoke, a short default bench
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_baseline_sizes.py -q -m gpu -x -s -k "exact" 2>&1 | grep -i "P3M 128\|near pairs\|passed\|failed\|rror" | head -4
-NB_P3M_NEAR=1 python -m pytest tests/test_gpu_force.py tests/test_gpu_dist.py tests/test_gpu_force_large.py -q -m gpu -x 2>&1 | tail -2
-NB_P3M_NEAR=1 python bench.py --steps 5 --warmup 3 --no-secondary --no-cpu > gpurun_out/r3a_bench_near1.json 2> gpurun_out/r3a.err || tail -3 gpurun_out/r3a.err
-python - <<PY
+python -m pytest tests -q -m gpu -x 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/last_bench.json 2> gpurun_out/last_bench.err; tail -c 300 gpurun_out/last_bench.err
+python -c "
 import json
-d=json.loads(open("gpurun_out/r3a_bench_near1.json").read().strip().splitlines()[-1])
-print("near 1:", round(d["ms_per_step"],2), round(d["phase_ms"]["p3m_short"],2), d["roofline"].get("exact_mode"))
-PY
+d=json.loads(open('gpurun_out/last_bench.json').read().strip().splitlines()[-1])
+print(d['ms_per_step'], d['e2e']['ms_per_step'], d['roofline'].get('exact_mode',{}).get('ms'))"
