@@ -864,8 +864,8 @@ class DistForceStepper:
             self._side = torch.cuda.Stream(device=dev)
         main = torch.cuda.current_stream(dev)
         pos, mom = self._pbuf[:n], self._mbuf[:n]
-        self._side.wait_stream(main)                      # earlier readers of the momentum buffer are done
         pos.copy_(hpos, non_blocking=True)
+        self._side.wait_stream(main)                      # behind the position upload (and earlier readers of mom)
         with torch.cuda.stream(self._side):
             mom.copy_(hmom, non_blocking=True)
         pos2, mom2 = self.step(pos, mom, dt_kick, dt_drift, mark=mark, n_total=n_total, periodic_pp=periodic_pp,
