@@ -1,10 +1,10 @@
 #!/bin/bash
-# scratch driver for one gpurun call (development only): the other three workloads
+# scratch driver for one gpurun call (development only): full GPU suite, smoke, a short default bench
 mkdir -p gpurun_out
-for w in pk pm pp; do
-  python bench.py --workload $w --steps 3 --warmup 3 --no-cpu > gpurun_out/r2final_bench_$w.json 2> gpurun_out/r2final_$w.err || tail -c 600 gpurun_out/r2final_$w.err
-  python -c "
+python -m pytest tests -q -m gpu -x 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/last_bench.json 2> gpurun_out/last_bench.err; tail -c 300 gpurun_out/last_bench.err
+python -c "
 import json
-d=json.loads(open('gpurun_out/r2final_bench_$w.json').read().strip().splitlines()[-1])
-print('$w', d['ms_per_step'], d['value'], d['e2e']['ms_per_step'], d['roofline']['kernel'][:30], round(d['roofline']['frac'],3))"
-done
+d=json.loads(open('gpurun_out/last_bench.json').read().strip().splitlines()[-1])
+print(d['ms_per_step'], d['e2e']['ms_per_step'], d['roofline'].get('exact_mode',{}).get('ms'))"
