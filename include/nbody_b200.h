@@ -221,6 +221,12 @@ int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, double cell, in
                      const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
                      int interlace_up, int interlace_down, double pref, float* force3,
                      float* force3_shifted, void* stream);
+/* nb_pm_force_mesh from meshes the caller has deposited already (nb_cic_deposit: float32, counts; rho_shifted = the
+ * deposit with shift = cell/2, NULL without upstream interlacing).  Used by the host-buffer step, which deposits each
+ * chunk of positions while the next one is still being uploaded.  The meshes are read, not changed. */
+int nb_pm_force_mesh_rho(nb_ctx* ctx, const float* rho, const float* rho_shifted, int N, const double* k_vals,
+                         const double* sinc_tab, double r_s, int deconv_order, int interlace_down, double pref,
+                         float* force3, float* force3_shifted, void* stream);
 
 /* ---- K4  PP direct sum -------------------------------------------------------------------
  * No reference source (CONCEPT PP; only its run time is in PPPMP3M/pppmp3mplotter.py:18-19).

@@ -48,6 +48,8 @@ PROTOTYPES = {
     "nb_kspace_fused": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_f64, c_i32, c_f64, c_vp, c_vp, c_vp]),
     "nb_pm_force_mesh": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_i32, c_vp, c_vp, c_f64, c_i32, c_i32, c_i32, c_f64,
                                  c_vp, c_vp, c_vp]),
+    "nb_pm_force_mesh_rho": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_f64, c_i32, c_i32, c_f64, c_vp, c_vp,
+                                     c_vp]),
     "nb_pp_pack": (c_i32, [c_vp, c_vp, c_i64, c_f64, c_f64, c_f64, c_f64, c_vp, c_vp, c_vp]),
     "nb_pp_accel": (c_i32, [c_vp, c_vp, c_i64, c_vp, c_i64, c_f64, c_f64, c_f64, c_i32, c_i32, c_vp, c_vp]),
     "nb_pp_near_fix": (c_i32, [c_vp, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_i32, c_f64, c_f64, c_f64, c_f64, c_f64, c_f64, c_f64,

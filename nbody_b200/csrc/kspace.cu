@@ -134,11 +134,12 @@ extern "C" int nb_kspace_fused_slab(nb_ctx* ctx, const void* rho1, const void* r
 // Single-GPU long-range solve: deposit -> R2C -> [shifted deposit -> R2C] -> K2 -> 3 (6) C2R.
 // force3 (and force3_shifted when interlace_down) receive 3·N³ float32 each, in units of
 // pref · counts (the caller folds 4πG·m/cell³/N³ into pref).
-extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N,
-                                const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
-                                int interlace_up, int interlace_down, double pref, float* force3,
-                                float* force3_shifted, void* stream) {
-  NB_REQUIRE(ctx && pos && k_vals && sinc_tab && force3, "NULL argument");
+// rho1_in / rho2_in: meshes the caller has deposited already (nb_pm_force_mesh_rho), else deposited here from pos.
+static int pm_force_mesh_impl(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N,
+                              const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                              int interlace_up, int interlace_down, double pref, float* force3,
+                              float* force3_shifted, const float* rho1_in, const float* rho2_in, void* stream) {
+  NB_REQUIRE(ctx && (pos || rho1_in) && k_vals && sinc_tab && force3, "NULL argument");
   NB_REQUIRE(!interlace_down || force3_shifted, "interlace_down needs force3_shifted");
   NB_REQUIRE(N >= 2, "bad N");
   cudaStream_t st = (cudaStream_t)stream;
@@ -155,21 +156,21 @@ extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, doub
   cufftHandle fwd, inv;
   if ((rc = nb_plan3d(ctx, N, CUFFT_R2C, st, &fwd))) return rc;
   if ((rc = nb_plan3d(ctx, N, CUFFT_C2R, st, &inv))) return rc;
-  {
+  if (!rho1_in) {
     NbPhase ph(ctx, NB_PH_DEPOSIT, st);
     if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.0, 0, nullptr, stream))) return rc;
   }
   {
     NbPhase ph(ctx, NB_PH_FFT_FWD, st);
-    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)rho, (cufftComplex*)s1));
+    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)(rho1_in ? const_cast<float*>(rho1_in) : (float*)rho), (cufftComplex*)s1));
   }
   if (interlace_up) {
-    {
+    if (!rho2_in) {
       NbPhase ph(ctx, NB_PH_DEPOSIT, st);
       if ((rc = nb_cic_deposit(ctx, pos, np, cell, N, rho, NB_F32, 0.5 * cell, 0, nullptr, stream))) return rc;
     }
     NbPhase ph(ctx, NB_PH_FFT_FWD, st);
-    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)rho, (cufftComplex*)s2));
+    NB_CHECK_CUFFT(cufftExecR2C(fwd, (cufftReal*)(rho2_in ? const_cast<float*>(rho2_in) : (float*)rho), (cufftComplex*)s2));
   }
   {
     NbPhase ph(ctx, NB_PH_KSPACE, st);
@@ -187,4 +188,25 @@ extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, doub
                             n3 * sizeof(float), st)))
         return rc;
   return NB_OK;
+}
+
+extern "C" int nb_pm_force_mesh(nb_ctx* ctx, const double* pos, int64_t np, double cell, int N,
+                                const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                                int interlace_up, int interlace_down, double pref, float* force3,
+                                float* force3_shifted, void* stream) {
+  NB_REQUIRE(pos != nullptr, "NULL argument");
+  return pm_force_mesh_impl(ctx, pos, np, cell, N, k_vals, sinc_tab, r_s, deconv_order, interlace_up, interlace_down,
+                            pref, force3, force3_shifted, nullptr, nullptr, stream);
+}
+
+// The same solve from meshes the caller has deposited (nb_cic_deposit, float32, counts; rho_shifted = the deposit
+// with shift = cell/2, or NULL without upstream interlacing): a host-buffer step deposits each chunk of positions
+// as it arrives, while the rest is still on the link.  The meshes are read, not changed.
+extern "C" int nb_pm_force_mesh_rho(nb_ctx* ctx, const float* rho, const float* rho_shifted, int N,
+                                    const double* k_vals, const double* sinc_tab, double r_s, int deconv_order,
+                                    int interlace_down, double pref, float* force3, float* force3_shifted,
+                                    void* stream) {
+  NB_REQUIRE(rho != nullptr, "NULL argument");
+  return pm_force_mesh_impl(ctx, nullptr, 0, 0.0, N, k_vals, sinc_tab, r_s, deconv_order, rho_shifted != nullptr,
+                            interlace_down, pref, force3, force3_shifted, rho, rho_shifted, stream);
 }

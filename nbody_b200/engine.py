@@ -398,6 +398,20 @@ class Engine:
                    "nb_pm_force_mesh")
         return out, (out_shifted if interlace_down else None)
 
+    def pm_force_mesh_from_rho(self, rho: torch.Tensor, rho_shifted, L: float, N: int, r_s: float, deconv_order: int,
+                               interlace_down: bool, pref: float, out: torch.Tensor, out_shifted=None):
+        """pm_force_mesh from float32 count meshes the caller has deposited (cic_deposit with shift 0 / cell/2)."""
+        kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))
+        s = self.sinc_tab(N, L)
+        for g in (rho, rho_shifted):
+            if g is not None and (g.dtype != torch.float32 or g.shape != (N, N, N) or not g.is_contiguous()):
+                raise ValueError("rho meshes must be contiguous (N,N,N) float32")
+        _lib.check(self.lib.nb_pm_force_mesh_rho(self.ctx, _ptr(rho), _ptr(rho_shifted), int(N), _ptr(kv), _ptr(s),
+                                                 float(r_s), int(deconv_order), int(bool(interlace_down)), float(pref),
+                                                 _ptr(out), _ptr(out_shifted) if interlace_down else C.c_void_p(0),
+                                                 self.stream), "nb_pm_force_mesh_rho")
+        return out, (out_shifted if interlace_down else None)
+
     def kspace_fused(self, rho1, rho2, L, N, r_s, deconv_order, pref, want_shifted=False):
         """K2 alone on caller-provided half spectra (complex64 [N][N][N/2+1])."""
         kv = self.table(("kv", N, float(L)), lambda: tables.k_vals(N, L))

@@ -60,6 +60,9 @@ class ForceStepper:
         self.overlap_min_particles = 1 << 26
         self.p3m_sms = int(os.environ.get("NB_P3M_SMS", "0"))      # 0: 0.595 x the device's SM count (88 of 148)
         self.p3m_delay_us = int(os.environ.get("NB_P3M_DELAY_US", "40"))
+        self.p3m_sms_predeposited = int(os.environ.get("NB_P3M_SMS_HOST", "0"))   # 0: 1.07 x p3m_sms
+        self.host_predeposit = os.environ.get("NB_HOST_PREDEPOSIT", "1") == "1"
+        self.host_predeposit_min = 1 << 22        # particles; below, one upload and the plain mesh solve
         self._acc_s = None
         self._streams = None
 
@@ -78,12 +81,16 @@ class ForceStepper:
         return self._force, self._force_s
 
     # -- pieces ---------------------------------------------------------------------------
-    def pm_mesh(self, pos):
+    def pm_mesh(self, pos, rho=None):
         """Long-range force meshes (acceleration per unit... in the caller's units)."""
         c = self.cfg
         N = c.gridsize
         f, fs = self._force_bufs()
         pref = 4.0 * math.pi * c.G * c.mass / c.cell ** 3 / float(N) ** 3
+        if rho is not None:           # meshes deposited by the caller (step_host: chunk by chunk under the upload)
+            self.eng.pm_force_mesh_from_rho(rho[0], rho[1], c.boxsize, N, c.r_s, c.deconv_order, bool(c.interlace[1]),
+                                            pref, f, fs)
+            return f, fs
         self.eng.pm_force_mesh(pos, c.boxsize, N, r_s=c.r_s, deconv_order=c.deconv_order,
                                interlace_up=bool(c.interlace[0]), interlace_down=bool(c.interlace[1]),
                                pref=pref, out=f, out_shifted=fs)
@@ -147,7 +154,7 @@ class ForceStepper:
         if join:
             main.wait_stream(cs)
 
-    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None, join=True):
+    def _p3m_fused(self, pos, mom, acc_out, kick, drift, tail_waits=None, host_out=None, join=True, rho=None):
         """Cell sort + pair kernel into a separate buffer, mesh chain, then ONE fused kernel:
         g = gather(mesh) + short; acc_out <- g and/or kick + drift.  With self.overlap the two
         parts run on two streams and two disjoint sets of SMs."""
@@ -168,7 +175,9 @@ class ForceStepper:
             # the memory-bound mesh chain runs on the others: FP32-bound and HBM-bound halves of the step side by
             # side.  The pair kernel must find the GPU idle when it starts (a CTA that exits on a foreign SM is not
             # replaced): the cell sort runs alone, and the mesh stream starts with a short delay kernel.
-            eng.p3m_set_sm_limit(self.p3m_sms)
+            # with the deposits done already (rho) the mesh side is shorter: the pair kernel gets more of the SMs
+            eng.p3m_set_sm_limit(self.p3m_sms if rho is None else
+                                 (self.p3m_sms_predeposited or round(self.p3m_sms * 1.07)))
             try:
                 with torch.cuda.stream(sr_stream):
                     sorted4, perm, cell_start = eng.cell_sort(pos, c.boxsize, self.ncs, mass=1.0)
@@ -179,7 +188,7 @@ class ForceStepper:
                 pm_stream.wait_event(sorted_ev)
                 with torch.cuda.stream(pm_stream):
                     eng.delay_us(self.p3m_delay_us)
-                    f, fs = self.pm_mesh(pos)
+                    f, fs = self.pm_mesh(pos, rho=rho)
                     eng.p3m_mesh_done()
             finally:
                 eng.p3m_set_sm_limit(0)
@@ -189,7 +198,7 @@ class ForceStepper:
             main.wait_stream(sr_stream)
         else:
             self.short_range(pos, self._acc_s, accumulate=False)
-            f, fs = self.pm_mesh(pos)
+            f, fs = self.pm_mesh(pos, rho=rho)
         if tail_waits is not None:            # e.g. the momentum upload of step_host
             main.wait_stream(tail_waits)
         if host_out is not None and mom is not None and acc_out is None:
@@ -272,6 +281,33 @@ class ForceStepper:
         return pos, mom
 
 
+    def _upload_and_deposit(self, hpos, dpos, chunks=8):
+        """Position upload in chunks on the current stream; on a second stream each chunk is deposited into the
+        (two, with upstream interlacing) density meshes as soon as it has arrived, so the deposits - 11 ms of the mesh
+        chain at config 5 - are done when the last chunk lands instead of starting then.  Returns the meshes."""
+        c, eng = self.cfg, self.eng
+        dev, N = eng.device, c.gridsize
+        if getattr(self, "_rho", None) is None:
+            self._rho = [torch.empty((N, N, N), dtype=torch.float32, device=dev),
+                         torch.empty((N, N, N), dtype=torch.float32, device=dev) if c.interlace[0] else None]
+            self._dep_stream = torch.cuda.Stream(device=dev)
+        main, dep = torch.cuda.current_stream(dev), self._dep_stream
+        dep.wait_stream(main)                       # the previous step's transforms are done reading the meshes
+        n = hpos.shape[0]
+        step = max(1, -(-n // chunks))
+        for a in range(0, n, step):
+            b = min(n, a + step)
+            dpos[a:b].copy_(hpos[a:b], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            dep.wait_event(ev)
+            with torch.cuda.stream(dep):
+                eng.cic_deposit(dpos[a:b], c.cell, N, out=self._rho[0], accumulate=a > 0)
+                if self._rho[1] is not None:
+                    eng.cic_deposit(dpos[a:b], c.cell, N, out=self._rho[1], shift=0.5 * c.cell, accumulate=a > 0)
+        main.wait_stream(dep)
+        return self._rho
+
     def step_host_pipelined(self, hpos: torch.Tensor, hmom: torch.Tensor, out_pos: torch.Tensor, out_mom: torch.Tensor,
                             dt_kick: float, dt_drift: float):
         """step_host for a stream of INDEPENDENT particle sets (PM / P3M): two sets of device buffers, so the upload of
@@ -341,7 +377,11 @@ class ForceStepper:
             self._dmom = torch.empty((n, 3), dtype=torch.float64, device=dev)
             self._side = torch.cuda.Stream(device=dev)
         main = torch.cuda.current_stream(dev)
-        self._dpos.copy_(hpos, non_blocking=True)
+        rho = None
+        if self.host_predeposit and self.cfg.method in ("pm", "p3m") and n >= self.host_predeposit_min:
+            rho = self._upload_and_deposit(hpos, self._dpos)
+        else:
+            self._dpos.copy_(hpos, non_blocking=True)
         # the momenta go up behind the positions, not beside them: two uploads released at the same moment (calls
         # enqueued back to back) share the link and the force computation starts late (measured: +20 ms per call)
         self._side.wait_stream(main)          # ... and the previous step is done with _dmom
@@ -351,7 +391,7 @@ class ForceStepper:
         kick = c.mass * dt_kick
         drift = dt_drift / (c.mass * c.a * c.a)
         if c.method == "pm":
-            f, fs = self.pm_mesh(self._dpos)
+            f, fs = self.pm_mesh(self._dpos, rho=rho)
             main.wait_stream(self._side)
             self._tail_to_host(lambda a, b: self.eng.gather_kick_drift(f, fs, c.gridsize, c.cell, self._dpos[a:b],
                                                                        self._dmom[a:b], None, 1.0, kick, drift,
@@ -360,7 +400,7 @@ class ForceStepper:
             return out_pos, out_mom
         elif self.fused_tail:
             self._p3m_fused(self._dpos, self._dmom, None, kick, drift, tail_waits=self._side,
-                            host_out=(out_pos, out_mom))
+                            host_out=(out_pos, out_mom), rho=rho)
             return out_pos, out_mom
         else:
             acc = self.accel(self._dpos, periodic_pp)

@@ -214,7 +214,9 @@ def test_step_host_matches_resident_step(F, method):
     hmom = torch.from_numpy(mom).pin_memory()
     opos = torch.empty_like(hpos).pin_memory()
     omom = torch.empty_like(hmom).pin_memory()
-    for rep in range(2):
+    for rep in range(3):
+        # third pass: positions uploaded in chunks with the deposits under the upload (the large-N form of step_host)
+        st.host_predeposit_min = 0 if rep == 2 else 1 << 40
         dp, dm = eng.to_device(pos), eng.to_device(mom)
         st.step(dp, dm, 0.3, 0.7)
         st.step_host(hpos, hmom, opos, omom, 0.3, 0.7)
