@@ -406,7 +406,7 @@ def bind_host_near_device(device_index: int):
         except (OSError, ValueError):
             node = -1
         return {"cpus": len(use), "numa_node": node}
-    except (OSError, ValueError, AttributeError, RuntimeError):
+    except Exception:      # no CUDA device, no sysfs entry, cpuset that forbids the change: leave everything as it is
         return None
 
 

@@ -156,3 +156,12 @@ def test_layout_errors():
         SlabLayout(4, 4, 0)          # 1 plane per rank < 2 ghost planes
     lay = SlabLayout(16, 4, 3)
     assert (lay.x0, lay.nxl, lay.y0, lay.nyl, lay.nzh, lay.rows) == (12, 4, 12, 4, 9, 36)
+
+
+def test_bind_host_near_device_leaves_the_process_alone_when_it_cannot_read_the_topology():
+    """No CUDA device here: the helper returns None and the CPU affinity of the process is unchanged."""
+    import os
+    from nbody_b200.dist import bind_host_near_device
+    before = os.sched_getaffinity(0)
+    assert bind_host_near_device(0) is None
+    assert os.sched_getaffinity(0) == before
